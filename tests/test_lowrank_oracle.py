@@ -1,0 +1,72 @@
+"""Engine math vs fp64 restatements."""
+import torch
+
+from dinunet_implementations_b200.distrib import lowrank as lr
+
+
+def test_orthogonalize_orthonormal_and_rank_deficient():
+    torch.manual_seed(0)
+    P = torch.randn(200, 6, dtype=torch.float64)
+    Q = lr.orthogonalize(P)
+    assert torch.allclose(Q.t() @ Q, torch.eye(6, dtype=torch.float64), atol=1e-10)
+    # span preserved
+    assert torch.allclose(Q @ (Q.t() @ P), P, atol=1e-9)
+    P[:, 3] = P[:, 0] * 2  # rank deficient: that column must vanish, not explode
+    Q = lr.orthogonalize(P)
+    assert Q[:, 3].abs().max() < 1e-6 and torch.isfinite(Q).all()
+
+
+def test_dad_exact_when_batch_le_rank():
+    torch.manual_seed(1)
+    D, A = torch.randn(8, 30, dtype=torch.float64), torch.randn(8, 20, dtype=torch.float64)
+    d, a, used = lr.dad_compress(D, A, rank=10)
+    assert used == 0
+    assert torch.allclose(lr.dad_reconstruct(d, a), D.t() @ A, atol=1e-12)
+
+
+def test_dad_exact_when_true_rank_le_r():
+    torch.manual_seed(2)
+    # 64 samples but the gradient has rank 4
+    basis_d, basis_a = torch.randn(4, 30, dtype=torch.float64), torch.randn(4, 20, dtype=torch.float64)
+    c = torch.randn(64, 4, dtype=torch.float64)
+    D, A = c @ basis_d, torch.linalg.qr(torch.randn(64, 64, dtype=torch.float64))[0][:, :4] @ basis_a
+    G = D.t() @ A
+    d, a, _ = lr.dad_compress(D, A, rank=10, num_pow_iters=3, tol=0.0)
+    assert torch.allclose(lr.dad_reconstruct(d, a), G, atol=1e-8 * G.abs().max())
+
+
+def test_dad_is_best_rank_r_after_enough_iters():
+    torch.manual_seed(3)
+    D, A = torch.randn(64, 40, dtype=torch.float64), torch.randn(64, 50, dtype=torch.float64)
+    G = D.t() @ A
+    d, a, _ = lr.dad_compress(D, A, rank=10, num_pow_iters=60, tol=0.0)
+    err = (lr.dad_reconstruct(d, a) - G).norm()
+    s = torch.linalg.svdvals(G)
+    best = s[10:].pow(2).sum().sqrt()
+    assert err <= best * 1.02
+
+
+def test_dad_reduce_equals_sum_of_site_grads_when_low_rank():
+    torch.manual_seed(4)
+    sites = []
+    for s in range(3):
+        D, A = torch.randn(3, 16, dtype=torch.float64), torch.randn(3, 12, dtype=torch.float64)
+        sites.append(lr.dad_compress(D, A, rank=10)[:2] + (D.t() @ A,))
+    d, a, _ = lr.dad_reduce([x[0] for x in sites], [x[1] for x in sites], rank=10, num_pow_iters=4, tol=0.0)
+    mean_G = sum(x[2] for x in sites) / 3
+    assert torch.allclose(lr.dad_reconstruct(d, a), mean_G, atol=1e-8)
+
+
+def test_powersgd_residual_plus_approx_is_input_and_exact_for_low_rank():
+    torch.manual_seed(5)
+    S, n, m, r = 4, 48, 32, 4
+    Ms = [torch.randn(n, m, dtype=torch.float64) for _ in range(S)]
+    Q0 = lr.psgd_init_q((n, m), r, seed=7, dtype=torch.float64)
+    M_hat, Es, Q = lr.psgd_oracle_step(Ms, [Q0] * S, r)
+    for M, E in zip(Ms, Es):
+        assert torch.allclose(M_hat + E, M, atol=1e-12)
+    # low-rank mean gradient: one step with warm Q recovers it exactly after two steps
+    U, V = torch.randn(n, 2, dtype=torch.float64), torch.randn(m, 2, dtype=torch.float64)
+    Ms = [U @ V.t() for _ in range(S)]
+    M_hat, _, Q = lr.psgd_oracle_step(Ms, [Q0] * S, r)
+    assert torch.allclose(M_hat, U @ V.t(), atol=1e-8)
