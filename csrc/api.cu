@@ -1,0 +1,180 @@
+// Host-side runtime pieces of libdinunet_b200: error reporting, device-memory arena +
+// CUDA-IPC peer mapping (the symmetric-memory substrate the fused aggregation kernels use),
+// TMA descriptor encoding, and the threaded CPU reducer used by the COINSTAC file mode.
+#include "common.cuh"
+
+#include <stdarg.h>
+
+#include <atomic>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "../include/dinunet_b200.h"
+
+// ------------------------------------------------------------------------------------ errors
+static thread_local char g_err[1024] = {0};
+static std::atomic<long long> g_launches{0};
+
+void dnb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+DNB_EXPORT const char* dnb_last_error(void) { return g_err; }
+DNB_EXPORT int dnb_version(void) { return 100; }
+
+void dnb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+DNB_EXPORT long long dnb_launch_count(void) { return g_launches.load(); }
+DNB_EXPORT void dnb_reset_launch_count(void) { g_launches.store(0); }
+
+// ------------------------------------------------------------------------------------ arena / IPC
+// The arena is plain cudaMalloc memory so that cudaIpcGetMemHandle describes exactly this
+// allocation (torch's caching allocator sub-allocates, which would need base+offset games).
+DNB_EXPORT int dnb_arena_alloc(size_t bytes, void** out) {
+    DNB_REQUIRE(out != nullptr, "dnb_arena_alloc: out is null");
+    DNB_CUDA_CHECK(cudaMalloc(out, bytes));
+    DNB_CUDA_CHECK(cudaMemset(*out, 0, bytes));
+    DNB_CUDA_CHECK(cudaDeviceSynchronize());
+    return 0;
+}
+DNB_EXPORT int dnb_arena_free(void* p) {
+    DNB_CUDA_CHECK(cudaFree(p));
+    return 0;
+}
+DNB_EXPORT int dnb_ipc_handle_size(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+DNB_EXPORT int dnb_ipc_get_handle(void* dptr, void* handle_out) {
+    cudaIpcMemHandle_t h;
+    DNB_CUDA_CHECK(cudaIpcGetMemHandle(&h, dptr));
+    memcpy(handle_out, &h, sizeof(h));
+    return 0;
+}
+DNB_EXPORT int dnb_ipc_open_handle(const void* handle, void** out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    DNB_CUDA_CHECK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+DNB_EXPORT int dnb_ipc_close_handle(void* p) {
+    DNB_CUDA_CHECK(cudaIpcCloseMemHandle(p));
+    return 0;
+}
+DNB_EXPORT int dnb_enable_peer_access(int peer_device) {
+    int can = 0, dev = 0;
+    DNB_CUDA_CHECK(cudaGetDevice(&dev));
+    if (peer_device == dev) return 0;
+    DNB_CUDA_CHECK(cudaDeviceCanAccessPeer(&can, dev, peer_device));
+    DNB_REQUIRE(can, "device %d cannot access peer %d", dev, peer_device);
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();
+        return 0;
+    }
+    DNB_CUDA_CHECK(e);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ TMA descriptors
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    });
+    return fn;
+}
+
+// Row-major bf16 matrix [rows, cols] with leading dimension ld (elements); box = [box_rows, 64 cols]
+// (64 bf16 = 128 B = one swizzle-128B row).  Out-of-bounds elements read as zero.
+int dnb_make_tmap_bf16_2d(CUtensorMap* map, const void* base, long rows, long cols, long ld, int box_rows,
+                          int box_cols) {
+    PFN_encodeTiled enc = get_encode();
+    DNB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled unavailable (driver too old?)");
+    DNB_REQUIRE(((uintptr_t)base & 15) == 0, "TMA base pointer must be 16-byte aligned");
+    DNB_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes (ld=%ld)", ld);
+    DNB_REQUIRE(box_cols * 2 <= 128 && box_rows <= 256, "TMA box too large");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DNB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed: %d (rows=%ld cols=%ld ld=%ld)", (int)r, rows, cols,
+                ld);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ CPU reducer
+// Mean over `n_src` same-length arrays (fp32 or fp16 wire format) into fp32 — the aggregator's
+// job in COINSTAC file mode.  Replaces the reference's multiprocessing.Pool of numpy workers
+// (remote.py:20-21) with threads over contiguous chunks: no pickling, one pass over memory.
+static inline float half_bits_to_float(uint16_t h) {
+    uint32_t sign = (uint32_t)(h & 0x8000) << 16;
+    uint32_t exp = (h >> 10) & 0x1F;
+    uint32_t man = h & 0x3FF;
+    uint32_t f;
+    if (exp == 0) {
+        if (man == 0) {
+            f = sign;
+        } else {
+            exp = 127 - 15 + 1;
+            while (!(man & 0x400)) {
+                man <<= 1;
+                exp--;
+            }
+            man &= 0x3FF;
+            f = sign | (exp << 23) | (man << 13);
+        }
+    } else if (exp == 31) {
+        f = sign | 0x7F800000u | (man << 13);
+    } else {
+        f = sign | ((exp + 127 - 15) << 23) | (man << 13);
+    }
+    float out;
+    memcpy(&out, &f, 4);
+    return out;
+}
+
+DNB_EXPORT int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n, int is_half, float* out,
+                                int n_threads) {
+    DNB_REQUIRE(n_src > 0 && n >= 0 && out != nullptr, "dnb_cpu_mean_f32: bad arguments");
+    if (n_threads <= 0) {
+        n_threads = (int)std::thread::hardware_concurrency();
+        if (n_threads <= 0) n_threads = 4;
+        if (n_threads > 16) n_threads = 16;
+    }
+    if (n < (1 << 16)) n_threads = 1;
+    const float inv = 1.0f / (float)n_src;
+    auto work = [&](long long lo, long long hi) {
+        for (long long i = lo; i < hi; ++i) {
+            float acc = 0.f;
+            for (int s = 0; s < n_src; ++s)
+                acc += is_half ? half_bits_to_float(((const uint16_t*)srcs[s])[i]) : ((const float*)srcs[s])[i];
+            out[i] = acc * inv;
+        }
+    };
+    if (n_threads == 1) {
+        work(0, n);
+        return 0;
+    }
+    std::vector<std::thread> th;
+    long long per = (n + n_threads - 1) / n_threads;
+    for (int t = 0; t < n_threads; ++t) {
+        long long lo = t * per, hi = lo + per > n ? n : lo + per;
+        if (lo >= hi) break;
+        th.emplace_back(work, lo, hi);
+    }
+    for (auto& t : th) t.join();
+    return 0;
+}

@@ -1,0 +1,223 @@
+// K1 — dSGD aggregation fused with the optimiser (engine semantics §2.3 E2).
+//
+// One launch per training step on every GPU (= site).  Each GPU's gradient buffer, parameter
+// buffer and signal pad live in a symmetric arena that every peer has mapped (CUDA IPC over
+// NVLink/NVSwitch), so the kernel itself pulls the peers' gradients and pushes the updated
+// parameters; no NCCL call and no host round-trip sit between backward and the next forward.
+//
+//   start barrier  (system-scope release/acquire flags, one slot per (block, peer))
+//   two-shot mode : rank r owns shard r.  For its shard it sums the S sites' gradients in fixed
+//                   rank order, scales by 1/(S*loss_scale) (the reference's unweighted mean over
+//                   sites), applies Adam/SGD on the fp32 master values, and stores the *updated
+//                   parameters* (fp32, plus an optional bf16 shadow for the tensor-core kernels)
+//                   into every peer's parameter buffer.  Optimiser state is only ever touched
+//                   for the local shard.
+//   one-shot mode : for tiny payloads (FreeSurfer MLP: 0.24 MB) every rank reduces the whole
+//                   vector itself and updates only its own copy; one NVLink traversal, no
+//                   parameter broadcast.  Summation order is the same on all ranks, so all
+//                   sites stay bit-identical.
+//   end barrier    (peers' pushes have landed; gradient buffers may be overwritten)
+//
+// Wire format of the gradients: fp32, bf16 or fp16 (`precision_bits`, compspec.json:161-176).
+// opt = 2 turns the optimiser off and writes the reduced mean to `out` (all-reduce of the
+// powerSGD P/Q factors, aggregation micro-benchmark).
+#include "common.cuh"
+#include "../include/dinunet_b200.h"
+
+void dnb_count_launch(int n);
+
+namespace {
+
+constexpr int kMaxRanks = DNB_MAX_RANKS;
+constexpr int kMaxBlocks = DNB_SIGNAL_BLOCKS;
+constexpr int kThreads = 512;
+
+struct DsgdArgs {
+    const void* grads[kMaxRanks];
+    float* params[kMaxRanks];
+    __nv_bfloat16* shadow[kMaxRanks];
+    uint32_t* flags[kMaxRanks];
+    float* m;
+    float* v;
+    float* out;
+    long long n;
+    int nranks, rank, mode, opt, use_flags;
+    float lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, momentum;
+    uint32_t epoch;
+};
+
+__device__ __forceinline__ void flag_barrier(const DsgdArgs& a, int phase) {
+    // Every block pairs up with the same-index block on each peer.
+    __syncthreads();
+    if (threadIdx.x < a.nranks) {
+        const int peer = threadIdx.x;
+        const size_t slot = ((size_t)phase * kMaxBlocks + blockIdx.x) * kMaxRanks;
+        dnb::st_release_sys(a.flags[peer] + slot + a.rank, a.epoch);
+        const uint32_t* mine = a.flags[a.rank] + slot + peer;
+        const long long t0 = clock64();
+        while ((int32_t)(dnb::ld_acquire_sys(mine) - a.epoch) < 0) {
+            if (clock64() - t0 > dnb::kSpinBudgetCycles) {
+                printf("dnb: dSGD flag barrier timed out (rank %d waits for %d, block %d, phase %d, epoch %u)\n",
+                       a.rank, peer, blockIdx.x, phase, a.epoch);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
+template <int WIRE>
+__device__ __forceinline__ void load8(const void* base, long long i, float (&x)[8]) {
+    if constexpr (WIRE == 0) {
+        const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + i);
+        float4 a = p[0], b = p[1];
+        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+        x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+    } else {
+        uint4 raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(base) + i);
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if constexpr (WIRE == 1) {
+                x[2 * k] = __uint_as_float(w[k] << 16);
+                x[2 * k + 1] = __uint_as_float(w[k] & 0xFFFF0000u);
+            } else {
+                __half2 h = *reinterpret_cast<const __half2*>(&w[k]);
+                float2 f = __half22float2(h);
+                x[2 * k] = f.x;
+                x[2 * k + 1] = f.y;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void store8_f32(float* base, long long i, const float (&x)[8]) {
+    float4* p = reinterpret_cast<float4*>(base + i);
+    p[0] = make_float4(x[0], x[1], x[2], x[3]);
+    p[1] = make_float4(x[4], x[5], x[6], x[7]);
+}
+
+template <int WIRE>
+__global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs a) {
+    if (a.use_flags) flag_barrier(a, 0);
+
+    long long lo = 0, hi = a.n;
+    if (a.mode == 0 && a.nranks > 1) {
+        long long per = ((a.n / 8 + a.nranks - 1) / a.nranks) * 8;
+        lo = per * a.rank;
+        hi = lo + per < a.n ? lo + per : a.n;
+        if (lo > hi) lo = hi;
+    }
+    const long long stride = (long long)gridDim.x * blockDim.x * 8;
+    for (long long i = lo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < hi; i += stride) {
+        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        // all peers' loads are issued before the first add: nranks 16-byte requests in flight
+        float x[kMaxRanks][8];
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+            if (r < a.nranks) load8<WIRE>(a.grads[r], i, x[r]);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+            if (r < a.nranks) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] += x[r][k];
+            }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= a.grad_scale;
+
+        if (a.opt == 2) {
+            store8_f32(a.out, i, g);
+            continue;
+        }
+        float p[8], m[8], v[8];
+        load8<0>(a.params[a.rank], i, p);
+        load8<0>(a.m, i, m);
+        if (a.opt == 0) {
+            load8<0>(a.v, i, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float gk = g[k] + a.wd * p[k];
+                m[k] = a.beta1 * m[k] + (1.f - a.beta1) * gk;
+                v[k] = a.beta2 * v[k] + (1.f - a.beta2) * gk * gk;
+                float mhat = m[k] / a.bc1;
+                float denom = sqrtf(v[k]) / a.bc2 + a.eps;   // bc2 = sqrt(1 - beta2^t), as torch.optim.Adam
+                p[k] -= a.lr * mhat / denom;
+            }
+            store8_f32(a.v, i, v);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float gk = g[k] + a.wd * p[k];
+                m[k] = a.momentum * m[k] + gk;
+                p[k] -= a.lr * (a.momentum != 0.f ? m[k] : gk);
+            }
+        }
+        store8_f32(a.m, i, m);
+        uint4 sh;
+        sh.x = dnb::pack_bf16x2(p[0], p[1]);
+        sh.y = dnb::pack_bf16x2(p[2], p[3]);
+        sh.z = dnb::pack_bf16x2(p[4], p[5]);
+        sh.w = dnb::pack_bf16x2(p[6], p[7]);
+        if (a.mode == 0) {
+#pragma unroll
+            for (int r = 0; r < kMaxRanks; ++r)
+                if (r < a.nranks) {
+                    store8_f32(a.params[r], i, p);
+                    if (a.shadow[r]) *reinterpret_cast<uint4*>(a.shadow[r] + i) = sh;
+                }
+        } else {
+            store8_f32(a.params[a.rank], i, p);
+            if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + i) = sh;
+        }
+    }
+    if (a.use_flags) flag_barrier(a, 1);
+}
+
+}  // namespace
+
+DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(d != nullptr, "dnb_dsgd_fused_step: null descriptor");
+    DNB_REQUIRE(d->nranks >= 1 && d->nranks <= kMaxRanks, "nranks must be in [1,%d], got %d", kMaxRanks, d->nranks);
+    DNB_REQUIRE(d->rank >= 0 && d->rank < d->nranks, "bad rank %d", d->rank);
+    DNB_REQUIRE(d->n % 8 == 0, "flat length must be padded to a multiple of 8 (got %lld)", d->n);
+    DNB_REQUIRE(d->wire >= 0 && d->wire <= 2, "wire dtype must be 0 (fp32), 1 (bf16) or 2 (fp16)");
+    DNB_REQUIRE(d->opt >= 0 && d->opt <= 2, "opt must be 0 (adam), 1 (sgd) or 2 (reduce only)");
+    DsgdArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int r = 0; r < d->nranks; ++r) {
+        a.grads[r] = d->grads[r];
+        a.params[r] = d->params[r];
+        a.shadow[r] = reinterpret_cast<__nv_bfloat16*>(d->shadow_bf16[r]);
+        a.flags[r] = d->flags[r];
+        DNB_REQUIRE(a.grads[r] != nullptr, "grads[%d] is null", r);
+        DNB_REQUIRE(d->opt == 2 || a.params[r] != nullptr, "params[%d] is null", r);
+    }
+    a.m = d->m; a.v = d->v; a.out = d->out;
+    a.n = d->n; a.nranks = d->nranks; a.rank = d->rank; a.mode = d->mode; a.opt = d->opt;
+    a.use_flags = d->use_flags && d->nranks > 1;
+    a.lr = d->lr; a.beta1 = d->beta1; a.beta2 = d->beta2; a.eps = d->eps; a.wd = d->weight_decay;
+    a.bc1 = 1.f - powf(d->beta1, (float)d->step);
+    a.bc2 = sqrtf(1.f - powf(d->beta2, (float)d->step));
+    a.grad_scale = d->grad_scale; a.momentum = d->momentum; a.epoch = d->epoch;
+    if (a.use_flags)
+        for (int r = 0; r < d->nranks; ++r) DNB_REQUIRE(a.flags[r] != nullptr, "flags[%d] is null", r);
+
+    long long span = a.n;
+    if (a.mode == 0 && a.nranks > 1) span = ((a.n / 8 + a.nranks - 1) / a.nranks) * 8;
+    int blocks = dnb_ceil_div(span, (long)kThreads * 8);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (blocks > sms) blocks = sms;           // one CTA per SM: all CTAs co-resident for the flag barrier
+    if (blocks > kMaxBlocks) blocks = kMaxBlocks;
+    if (blocks < 1) blocks = 1;
+    switch (d->wire) {
+        case 0: dsgd_fused_kernel<0><<<blocks, kThreads, 0, stream>>>(a); break;
+        case 1: dsgd_fused_kernel<1><<<blocks, kThreads, 0, stream>>>(a); break;
+        default: dsgd_fused_kernel<2><<<blocks, kThreads, 0, stream>>>(a); break;
+    }
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}

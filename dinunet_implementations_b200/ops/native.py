@@ -115,3 +115,61 @@ def reduce_mean_npy(paths):
     if rc != 0:
         return None
     return out
+
+
+# ----------------------------------------------------------------------- ctypes mirrors of include/dinunet_b200.h
+MAX_RANKS = 8
+SIGNAL_BLOCKS = 160
+SIGNAL_WORDS = 2 * SIGNAL_BLOCKS * MAX_RANKS
+
+
+class DsgdDesc(ctypes.Structure):
+    _fields_ = [
+        ("grads", ctypes.c_void_p * MAX_RANKS),
+        ("params", ctypes.c_void_p * MAX_RANKS),
+        ("shadow_bf16", ctypes.c_void_p * MAX_RANKS),
+        ("flags", ctypes.c_void_p * MAX_RANKS),
+        ("m", ctypes.c_void_p), ("v", ctypes.c_void_p), ("out", ctypes.c_void_p),
+        ("n", ctypes.c_longlong),
+        ("nranks", ctypes.c_int), ("rank", ctypes.c_int),
+        ("wire", ctypes.c_int), ("mode", ctypes.c_int), ("opt", ctypes.c_int),
+        ("use_flags", ctypes.c_int), ("step", ctypes.c_int),
+        ("lr", ctypes.c_float), ("beta1", ctypes.c_float), ("beta2", ctypes.c_float), ("eps", ctypes.c_float),
+        ("weight_decay", ctypes.c_float), ("momentum", ctypes.c_float),
+        ("grad_scale", ctypes.c_float),
+        ("epoch", ctypes.c_uint32),
+    ]
+
+
+class GemmDesc(ctypes.Structure):
+    _fields_ = [
+        ("A", ctypes.c_void_p), ("lda", ctypes.c_longlong),
+        ("B", ctypes.c_void_p), ("ldb", ctypes.c_longlong),
+        ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
+        ("out", ctypes.c_void_p), ("ldo", ctypes.c_longlong),
+        ("out_bf16", ctypes.c_int),
+        ("outT", ctypes.c_void_p), ("ldt", ctypes.c_longlong),
+        ("bias_n", ctypes.c_void_p), ("bias_m", ctypes.c_void_p),
+        ("mask", ctypes.c_void_p), ("ldmask", ctypes.c_longlong),
+        ("colsum", ctypes.c_void_p),
+        ("alpha", ctypes.c_float),
+        ("relu", ctypes.c_int), ("accumulate", ctypes.c_int), ("split_k", ctypes.c_int), ("block_n", ctypes.c_int),
+    ]
+
+
+def launch_count() -> int:
+    l = _try_load()
+    if l is None:
+        return 0
+    l.dnb_launch_count.restype = ctypes.c_longlong
+    return int(l.dnb_launch_count())
+
+
+def reset_launch_count():
+    l = _try_load()
+    if l is not None:
+        l.dnb_reset_launch_count()
+
+
+def _p(t):
+    return 0 if t is None else t.data_ptr()

@@ -1,0 +1,139 @@
+"""Comm substrate: a symmetric device-memory arena per site, mapped into every peer.
+
+``SiteGroup`` is what the fused aggregation kernels run on.  Two back ends:
+
+* **ipc** – one process per GPU (``torchrun``): every rank ``cudaMalloc``s an arena of the same
+  layout, exports it with CUDA IPC, exchanges the 64-byte handles once through
+  ``torch.distributed`` (bootstrap only — SURVEY §5.8: "the steady-state aggregation paths issue
+  no NCCL call") and opens its peers' arenas, so kernels address remote HBM directly over
+  NVLink/NVSwitch.
+* **local** – S simulated sites inside one process on one GPU: S arenas in the same address
+  space.  The kernels are identical; only the cross-GPU flag barrier is switched off, because
+  kernels that wait for one another must not be launched back-to-back on one device.  This is
+  how the multi-site logic is tested on a single B200.
+
+The arena is carved by name (``alloc``) in the same order on every rank, so offsets agree.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from ..ops import native
+
+
+class _CudaView:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can alias arena memory."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def _as_tensor(ptr, nbytes, device):
+    return torch.as_tensor(_CudaView(ptr, nbytes), device=device)
+
+
+class SiteGroup:
+    def __init__(self, nsites: int, rank: int, arena_bytes: int, device, backend: str):
+        self.nsites, self.rank, self.arena_bytes, self.backend = int(nsites), int(rank), int(arena_bytes), backend
+        self.device = torch.device(device)
+        self.base = [0] * self.nsites          # base pointer of every site's arena in THIS process
+        self._owned = []
+        self._opened = []
+        self._cursor = 0
+        self._layout = {}
+        self.epoch = 0
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def local(cls, nsites: int, arena_bytes: int, device="cuda:0"):
+        lib = native.require_gpu()
+        g = cls(nsites, 0, arena_bytes, device, "local")
+        with torch.cuda.device(g.device):
+            for s in range(nsites):
+                p = ctypes.c_void_p()
+                native.check(lib.dnb_arena_alloc(ctypes.c_size_t(arena_bytes), ctypes.byref(p)), "arena_alloc")
+                g.base[s] = p.value
+                g._owned.append(p.value)
+        g._reserve_flags()
+        return g
+
+    @classmethod
+    def from_torch_distributed(cls, arena_bytes: int, device=None):
+        """One arena per rank; handles exchanged once with ``all_gather_object``."""
+        import torch.distributed as dist
+        lib = native.require_gpu()
+        rank, world = dist.get_rank(), dist.get_world_size()
+        device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        g = cls(world, rank, arena_bytes, device, "ipc" if world > 1 else "local")
+        with torch.cuda.device(device):
+            p = ctypes.c_void_p()
+            native.check(lib.dnb_arena_alloc(ctypes.c_size_t(arena_bytes), ctypes.byref(p)), "arena_alloc")
+            g.base[rank] = p.value
+            g._owned.append(p.value)
+            if world > 1:
+                hsz = lib.dnb_ipc_handle_size()
+                buf = ctypes.create_string_buffer(hsz)
+                native.check(lib.dnb_ipc_get_handle(p, buf), "ipc_get_handle")
+                handles = [None] * world
+                dist.all_gather_object(handles, (bytes(buf.raw), device.index))
+                for r, (h, dev_idx) in enumerate(handles):
+                    if r == rank:
+                        continue
+                    native.check(lib.dnb_enable_peer_access(ctypes.c_int(int(dev_idx))), "enable_peer_access")
+                    q = ctypes.c_void_p()
+                    native.check(lib.dnb_ipc_open_handle(ctypes.create_string_buffer(h, hsz), ctypes.byref(q)),
+                                 "ipc_open_handle")
+                    g.base[r] = q.value
+                    g._opened.append(q.value)
+                dist.barrier()
+        g._reserve_flags()
+        return g
+
+    def _reserve_flags(self):
+        self.flags = self.alloc("__flags__", native.SIGNAL_WORDS, torch.int32)
+
+    # ------------------------------------------------------------------ carving
+    def alloc(self, name: str, numel: int, dtype: torch.dtype, align: int = 256):
+        """Reserve ``numel`` elements at the same offset in every site's arena.
+
+        Returns the list of per-site tensors (index = site); in ipc mode entries for remote
+        sites alias peer memory and are meant for kernels, not for host-side torch ops.
+        """
+        esz = torch.empty(0, dtype=dtype).element_size()
+        off = (self._cursor + align - 1) // align * align
+        nbytes = int(numel) * esz
+        if off + nbytes > self.arena_bytes:
+            raise MemoryError(f"arena exhausted: need {off + nbytes} bytes, have {self.arena_bytes}")
+        self._cursor = off + nbytes
+        self._layout[name] = (off, int(numel), dtype)
+        return self.views(name)
+
+    def views(self, name):
+        off, numel, dtype = self._layout[name]
+        esz = torch.empty(0, dtype=dtype).element_size()
+        return [_as_tensor(b + off, numel * esz, self.device).view(dtype) for b in self.base]
+
+    def ptrs(self, name):
+        off = self._layout[name][0]
+        return [b + off for b in self.base]
+
+    def local_view(self, name, site=None):
+        return self.views(name)[self.rank if site is None else site]
+
+    def next_epoch(self):
+        self.epoch += 1
+        return self.epoch
+
+    @property
+    def use_flags(self):
+        return self.backend == "ipc"
+
+    def close(self):
+        l = native.lib()
+        for q in self._opened:
+            l.dnb_ipc_close_handle(ctypes.c_void_p(q))
+        for p in self._owned:
+            l.dnb_arena_free(ctypes.c_void_p(p))
+        self._opened, self._owned = [], []

@@ -1,0 +1,138 @@
+"""Device-mode dSGD: flat symmetric buffers + the fused reduce/optimiser kernel (K1).
+
+``FusedDSGD`` owns, inside a ``SiteGroup`` arena, one flat fp32 parameter buffer, one flat
+gradient buffer in the wire dtype (``precision_bits``: fp32 / bf16 / fp16) and optionally a
+bf16 shadow of the parameters for the tensor-core kernels.  ``bind`` re-points a module's
+parameters (and, for an fp32 wire, their ``.grad``) at slices of those buffers, so backward
+writes gradients straight into peer-visible memory and the updated weights appear in place —
+there is no gather, no file, no host copy between backward and the next forward.
+
+One ``step()`` = one kernel launch per site (``csrc/dsgd.cu``): cross-site barrier → mean of the
+sites' gradients → unscale → Adam/SGD → push updated parameters → barrier.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from ..ops import native
+from .comm import SiteGroup
+
+_WIRE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
+
+
+def wire_dtype_from_bits(precision_bits, prefer_bf16=True):
+    if str(precision_bits) == "16":
+        return torch.bfloat16 if prefer_bf16 else torch.float16
+    return torch.float32
+
+
+class FusedDSGD:
+    def __init__(self, group: SiteGroup, numel: int, wire_dtype=torch.float32, lr=1e-3, betas=(0.9, 0.999), eps=1e-8,
+                 weight_decay=0.0, optimizer="adam", momentum=0.0, shadow_bf16=False, mode="auto", loss_scale=1.0,
+                 name="dsgd"):
+        self.group = group
+        self.numel = int(numel)
+        self.n = (self.numel + 7) // 8 * 8
+        self.wire_dtype = wire_dtype
+        self.lr, self.betas, self.eps, self.weight_decay = float(lr), betas, float(eps), float(weight_decay)
+        self.opt = {"adam": 0, "sgd": 1, "none": 2}[optimizer]
+        self.momentum = float(momentum)
+        self.loss_scale = float(loss_scale)
+        # one-shot pull below ~1 MB of gradients (pure latency regime)
+        if mode == "auto":
+            mode = "one_shot" if self.n * 4 <= (1 << 20) else "two_shot"
+        self.mode = {"two_shot": 0, "one_shot": 1}[mode]
+        self.params = group.alloc(f"{name}.params", self.n, torch.float32)
+        self.grads = group.alloc(f"{name}.grads", self.n, wire_dtype)
+        self.shadow = group.alloc(f"{name}.shadow", self.n, torch.bfloat16) if shadow_bf16 else None
+        self._names = (f"{name}.params", f"{name}.grads", f"{name}.shadow" if shadow_bf16 else None)
+        dev = group.device
+        n_states = group.nsites if group.backend == "local" else 1
+        self.m = [torch.zeros(self.n, device=dev) for _ in range(n_states)]
+        self.v = [torch.zeros(self.n, device=dev) for _ in range(n_states)]
+        self.out = None
+        self.t = 0
+        self._descs = None
+        self._grad_staging = None   # per-site fp32 grads when the wire is 16-bit
+
+    # ------------------------------------------------------------------ module binding
+    def sites_here(self):
+        return list(range(self.group.nsites)) if self.group.backend == "local" else [self.group.rank]
+
+    def bind(self, module: torch.nn.Module, site=None):
+        """Move ``module``'s parameters into this site's flat buffer (values preserved)."""
+        site = self.group.rank if site is None else site
+        flat_p, flat_g = self.params[site], self.grads[site]
+        ps = [p for p in module.parameters() if p.requires_grad]
+        total = sum(p.numel() for p in ps)
+        if total != self.numel:
+            raise ValueError(f"module has {total} trainable values, FusedDSGD was sized for {self.numel}")
+        staging = None
+        if self.wire_dtype != torch.float32:
+            staging = torch.zeros(self.n, device=self.group.device)
+            self._grad_staging = self._grad_staging or {}
+            self._grad_staging[site] = staging
+        off = 0
+        with torch.no_grad():
+            for p in ps:
+                n = p.numel()
+                flat_p[off:off + n].copy_(p.detach().reshape(-1))
+                p.data = flat_p[off:off + n].view_as(p)
+                gsrc = flat_g if staging is None else staging
+                p.grad = gsrc[off:off + n].view_as(p)
+                off += n
+        if self.shadow is not None:
+            self.shadow[site].copy_(flat_p)
+        return ps
+
+    def pack_grads(self, site=None):
+        """16-bit wire only: cast the fp32 staging gradients into the peer-visible wire buffer."""
+        if self._grad_staging:
+            for s in ([site] if site is not None else self.sites_here()):
+                self.grads[s].copy_(self._grad_staging[s])
+
+    def zero_grad(self, site=None):
+        for s in ([site] if site is not None else self.sites_here()):
+            (self._grad_staging[s] if self._grad_staging else self.grads[s]).zero_()
+
+    # ------------------------------------------------------------------ the step
+    def _desc(self, site, state_ix):
+        d = native.DsgdDesc()
+        g = self.group
+        gp, pp = g.ptrs(self._names[1]), g.ptrs(self._names[0])
+        sp = g.ptrs(self._names[2]) if self._names[2] else [0] * g.nsites
+        fp = g.ptrs("__flags__")
+        for r in range(g.nsites):
+            d.grads[r], d.params[r], d.shadow_bf16[r], d.flags[r] = gp[r], pp[r], sp[r] or None, fp[r]
+        d.m, d.v = self.m[state_ix].data_ptr(), self.v[state_ix].data_ptr()
+        d.out = self.out.data_ptr() if self.out is not None else None
+        d.n, d.nranks, d.rank = self.n, g.nsites, site
+        d.wire, d.mode, d.opt = _WIRE[self.wire_dtype], self.mode, self.opt
+        d.use_flags = int(g.use_flags)
+        d.beta1, d.beta2, d.eps = self.betas[0], self.betas[1], self.eps
+        d.weight_decay, d.momentum = self.weight_decay, self.momentum
+        d.grad_scale = 1.0 / (g.nsites * self.loss_scale)
+        return d
+
+    def step(self, lr=None):
+        """Aggregate + update.  ipc: one launch on this rank.  local: one launch per simulated site."""
+        lib = native.require_gpu()
+        if self._descs is None:
+            self._descs = [self._desc(s, i) for i, s in enumerate(self.sites_here())]
+        self.pack_grads()
+        self.t += 1
+        epoch = self.group.next_epoch()
+        st = native.stream()
+        for d in self._descs:
+            d.step, d.epoch, d.lr = self.t, epoch, float(self.lr if lr is None else lr)
+            native.check(lib.dnb_dsgd_fused_step(ctypes.byref(d), st), "dnb_dsgd_fused_step")
+
+    def allreduce_mean(self, out: torch.Tensor):
+        """Reduce-only use of the same kernel: ``out = mean over sites of grads`` (local site)."""
+        assert self.opt == 2, "construct with optimizer='none'"
+        self.out = out
+        self._descs = None
+        self.step()
+        return out

@@ -1,0 +1,99 @@
+/* C ABI of libdinunet_b200.so — hand-written sm_100a kernels + the small host runtime
+ * around them.  No PyTorch dependency: callers pass raw device pointers and a CUDA stream.
+ * Python binds these through ctypes (dinunet_implementations_b200/ops/native.py).
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure dnb_last_error() describes why;
+ *   - `stream` is a cudaStream_t passed as void*;
+ *   - matrices are row-major; "ld" is the leading dimension in elements;
+ *   - kernels that wait on other GPUs or on mbarriers bound their spins and trap instead of
+ *     hanging.
+ *
+ * Reference citations give the math each entry point reproduces (paths relative to the
+ * reference tree).
+ */
+#ifndef DINUNET_B200_H
+#define DINUNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DNB_MAX_RANKS 8
+#define DNB_SIGNAL_BLOCKS 160
+/* uint32 slots a signal pad needs: 2 phases x blocks x ranks */
+#define DNB_SIGNAL_WORDS (2 * DNB_SIGNAL_BLOCKS * DNB_MAX_RANKS)
+
+/* ---- runtime ------------------------------------------------------------------------- */
+const char* dnb_last_error(void);
+int dnb_version(void);
+long long dnb_launch_count(void);      /* kernels launched by this library so far */
+void dnb_reset_launch_count(void);
+
+/* symmetric arena: cudaMalloc'ed, zeroed, exportable through CUDA IPC */
+int dnb_arena_alloc(size_t bytes, void** out);
+int dnb_arena_free(void* p);
+int dnb_ipc_handle_size(void);
+int dnb_ipc_get_handle(void* dptr, void* handle_out);
+int dnb_ipc_open_handle(const void* handle, void** out);
+int dnb_ipc_close_handle(void* p);
+int dnb_enable_peer_access(int peer_device);
+
+/* COINSTAC file mode: mean over n_src flat arrays (fp32, or fp16 when is_half) -> fp32.
+ * Replaces the aggregator's multiprocessing pool (reference remote.py:20-21). */
+int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n, int is_half, float* out, int n_threads);
+
+/* ---- K1: dSGD all-reduce fused with Adam/SGD (reference engine "dSGD", comps/__init__.py:14;
+ *      precision_bits compspec.json:161-176) ----------------------------------------------- */
+typedef struct DnbDsgdDesc {
+    const void* grads[DNB_MAX_RANKS];   /* every rank's flat gradient buffer (wire dtype), peer-mapped */
+    float* params[DNB_MAX_RANKS];       /* every rank's flat fp32 parameter buffer, peer-mapped */
+    void* shadow_bf16[DNB_MAX_RANKS];   /* optional bf16 copy of the parameters (NULL to skip) */
+    uint32_t* flags[DNB_MAX_RANKS];     /* every rank's signal pad, DNB_SIGNAL_WORDS uint32, zero-initialised */
+    float* m;                           /* local optimiser state, length n (Adam m / SGD momentum) */
+    float* v;                           /* local Adam v, length n */
+    float* out;                         /* opt == 2: reduced mean goes here */
+    long long n;                        /* flat length, multiple of 8 */
+    int nranks, rank;
+    int wire;                           /* 0 fp32, 1 bf16, 2 fp16 */
+    int mode;                           /* 0 two-shot (shard + push params), 1 one-shot (pull all) */
+    int opt;                            /* 0 Adam, 1 SGD(+momentum), 2 none (reduce only) */
+    int use_flags;                      /* 0: no cross-GPU barrier (single-GPU emulation of S sites) */
+    int step;                           /* optimiser step count t >= 1 (Adam bias correction) */
+    float lr, beta1, beta2, eps, weight_decay, momentum;
+    float grad_scale;                   /* 1 / (nranks * loss_scale) */
+    uint32_t epoch;                     /* strictly increasing per launch; barrier generation */
+} DnbDsgdDesc;
+int dnb_dsgd_fused_step(const DnbDsgdDesc* desc, void* stream);
+
+/* ---- tcgen05 + TMA GEMM with fused epilogue --------------------------------------------
+ * D[M,N] = alpha * A[M,K] * B[N,K]^T ; A and B bf16 row-major (lda, ldb multiples of 8),
+ * fp32 accumulation in TMEM.  Used for: encoder Linear+ReLU (reference comps/icalstm/models.py:87,107),
+ * LSTM input projection i2h for all timesteps (models.py:31), the wide FreeSurfer layers
+ * (comps/fs/models.py:13-25), their weight/data-gradient GEMMs, and the powerSGD products. */
+typedef struct DnbGemmDesc {
+    const void* A; long long lda;       /* [M,K] bf16 */
+    const void* B; long long ldb;       /* [N,K] bf16 */
+    int M, N, K;
+    void* out; long long ldo;           /* [M,N] fp32 or bf16 (may be NULL) */
+    int out_bf16;
+    void* outT; long long ldt;          /* optional transposed bf16 copy [N,M] */
+    const float* bias_n;                /* optional [N], added per column */
+    const float* bias_m;                /* optional [M], added per row */
+    const void* mask; long long ldmask; /* optional bf16 [M,N]: result zeroed where mask <= 0 (ReLU backward) */
+    float* colsum;                      /* optional [N]: += column sums of the result (bias gradient) */
+    float alpha;
+    int relu;
+    int accumulate;                     /* fp32 out += result (atomic) */
+    int split_k;                        /* >1: split the K loop over grid.z, needs plain fp32 out, pre-zeroed */
+    int block_n;                        /* 0 = auto, else 16/32/64/128 */
+} DnbGemmDesc;
+int dnb_gemm_bf16(const DnbGemmDesc* desc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DINUNET_B200_H */
