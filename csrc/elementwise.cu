@@ -1,0 +1,167 @@
+// Layout / cast kernels around the GEMMs, K10 window gather, K6 softmax + cross-entropy.
+#include "common.cuh"
+#include "../include/dinunet_b200.h"
+
+void dnb_count_launch(int n);
+
+namespace {
+
+// x fp32 [B, S, F]  ->  rows bf16 [S*B, ldr]  (row = t*B + b, "time-major")
+//                   and optionally colsT bf16 [F, ldt] (colsT[f][t*B+b]) — the K-major operand of
+//                   the encoder weight-gradient GEMM.  32x32 smem tile transpose.
+__global__ void cast_time_major_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ rows, long long ldr,
+                                       __nv_bfloat16* __restrict__ colsT, long long ldt, int B, int S, int F) {
+    __shared__ float tile[32][33];
+    const int r0 = blockIdx.y * 32, f0 = blockIdx.x * 32;
+    const int R = B * S;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, f = f0 + threadIdx.x;       // r = t*B + b
+        float v = 0.f;
+        if (r < R && f < F) {
+            const int t = r / B, b = r % B;
+            v = x[((long long)b * S + t) * F + f];
+            rows[(long long)r * ldr + f] = __float2bfloat16(v);
+        }
+        tile[i][threadIdx.x] = v;
+    }
+    if (colsT == nullptr) return;
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int f = f0 + i, r = r0 + threadIdx.x;
+        if (f < F && r < R) colsT[(long long)f * ldt + r] = __float2bfloat16(tile[threadIdx.x][i]);
+    }
+}
+
+__global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldi,
+                                      __nv_bfloat16* __restrict__ out, long long ldo, int R, int C) {
+    __shared__ __nv_bfloat16 tile[32][34];
+    const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < R && c < C) ? in[(long long)r * ldi + c] : __float2bfloat16(0.f);
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < C && r < R) out[(long long)c * ldo + r] = tile[threadIdx.x][i];
+    }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+    long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const long long stride = (long long)gridDim.x * blockDim.x * 4;
+    for (; i + 3 < n; i += stride) {
+        const float4 v = *reinterpret_cast<const float4*>(in + i);
+        uint2 p;
+        p.x = dnb::pack_bf16x2(v.x, v.y);
+        p.y = dnb::pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(out + i) = p;
+    }
+    if (i < n && i + 3 >= n)
+        for (long long k = i; k < n; ++k) out[k] = __float2bfloat16(in[k]);
+}
+
+// K10: [N, C, T] -> [N, S, C, W], window j = data[:, :, j*stride : j*stride+W]
+// (reference: the Python double loop in comps/icalstm/__init__.py:29-32)
+__global__ void window_gather_kernel(const float* __restrict__ in, float* __restrict__ out, int N, int C, int T,
+                                     int S, int W, int stride) {
+    const long long total = (long long)N * S * C * W;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int w = i % W;
+        const int c = (i / W) % C;
+        const int s = (i / ((long long)W * C)) % S;
+        const int n = i / ((long long)W * C * S);
+        out[i] = in[((long long)n * C + c) * T + s * stride + w];
+    }
+}
+
+// K6: softmax + cross-entropy (mean over the batch) forward, and its gradient, in one pass.
+// One warp per row; classes strided over lanes.  loss accumulated with one atomic per row.
+__global__ void softmax_ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                                  float* __restrict__ prob, float* __restrict__ dlogits, float* __restrict__ loss,
+                                  int B, int ncls, int log_softmax_out) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= B) return;
+    const float* z = logits + (long long)row * ncls;
+    float mx = -INFINITY;
+    for (int c = lane; c < ncls; c += 32) mx = fmaxf(mx, z[c]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int c = lane; c < ncls; c += 32) sum += __expf(z[c] - mx);
+    sum = dnb::warp_sum(sum);
+    const float lse = mx + __logf(sum);
+    const int y = (int)labels[row];
+    const float invB = 1.f / (float)B;
+    for (int c = lane; c < ncls; c += 32) {
+        const float p = __expf(z[c] - lse);
+        if (prob) prob[(long long)row * ncls + c] = log_softmax_out ? (z[c] - lse) : p;
+        if (dlogits) dlogits[(long long)row * ncls + c] = (p - (c == y ? 1.f : 0.f)) * invB;
+    }
+    if (lane == 0 && loss) atomicAdd(loss, (lse - z[y]) * invB);
+}
+
+}  // namespace
+
+DNB_EXPORT int dnb_cast_time_major(const float* x, void* rows, long long ldr, void* colsT, long long ldt, int B, int S,
+                                   int F, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(x && rows && B > 0 && S > 0 && F > 0, "dnb_cast_time_major: bad arguments");
+    dim3 grid((F + 31) / 32, (B * S + 31) / 32), block(32, 8);
+    cast_time_major_kernel<<<grid, block, 0, st>>>(x, reinterpret_cast<__nv_bfloat16*>(rows), ldr,
+                                                   reinterpret_cast<__nv_bfloat16*>(colsT), ldt, B, S, F);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+DNB_EXPORT int dnb_transpose_bf16(const void* in, long long ldi, void* out, long long ldo, int R, int C, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(in && out && R > 0 && C > 0, "dnb_transpose_bf16: bad arguments");
+    dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
+    transpose_bf16_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(in), ldi,
+                                                  reinterpret_cast<__nv_bfloat16*>(out), ldo, R, C);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+DNB_EXPORT int dnb_cast_f32_bf16(const float* in, void* out, long long n, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(in && out && n >= 0, "dnb_cast_f32_bf16: bad arguments");
+    DNB_REQUIRE(((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 7) == 0, "dnb_cast_f32_bf16: unaligned buffers");
+    if (n == 0) return 0;
+    int blocks = dnb_ceil_div(n, 256 * 4);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    cast_f32_bf16_kernel<<<blocks, 256, 0, st>>>(in, reinterpret_cast<__nv_bfloat16*>(out), n);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+DNB_EXPORT int dnb_window_gather(const float* in, float* out, int N, int C, int T, int S, int W, int stride,
+                                 void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(in && out, "dnb_window_gather: null buffer");
+    DNB_REQUIRE((long long)(S - 1) * stride + W <= T, "dnb_window_gather: windows exceed the time axis");
+    const long long total = (long long)N * S * C * W;
+    int blocks = dnb_ceil_div(total, 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    window_gather_kernel<<<blocks, 256, 0, st>>>(in, out, N, C, T, S, W, stride);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+DNB_EXPORT int dnb_softmax_ce(const float* logits, const long long* labels, float* prob, float* dlogits, float* loss,
+                              int B, int ncls, int log_softmax_out, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(logits && labels && B > 0 && ncls > 0, "dnb_softmax_ce: bad arguments");
+    if (loss) DNB_CUDA_CHECK(cudaMemsetAsync(loss, 0, sizeof(float), st));
+    softmax_ce_kernel<<<(B + 3) / 4, 128, 0, st>>>(logits, labels, prob, dlogits, loss, B, ncls, log_softmax_out);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}

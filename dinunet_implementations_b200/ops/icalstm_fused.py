@@ -1,9 +1,176 @@
-"""Fused sm_100a forward/backward of the ICA-LSTM (filled in by ops.lstm / ops.head)."""
+"""Fused sm_100a forward/backward of the whole ICA-LSTM (one ``autograd.Function``).
+
+Forward (7 launches): cast+time-major transpose → encoder GEMM(+bias+ReLU, +transposed copy)
+→ input-projection GEMM for all timesteps and both directions → persistent LSTM recurrence →
+classifier head.  Backward (11 launches): head → LSTM BPTT → transposes → tcgen05 weight- and
+data-gradient GEMMs (ReLU mask, bias column-sums and transposed store fused in the epilogue).
+
+Gradients are *accumulated* into ``param.grad`` (allocated on demand) — the same contract as
+autograd — and the Function returns no parameter gradients itself; the device engine points
+``param.grad`` at slices of the peer-visible flat gradient buffer, so the backward kernels write
+straight into the memory the fused dSGD kernel aggregates.
+
+bf16 copies of the weights come from the engine's parameter shadow when bound
+(``model._bf16_shadow``), otherwise they are cast per call.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import native
+from .native import vp
+from .gemm import gemm_bf16
+from .lstm import lstm_forward, lstm_backward, lstm_supported
+from .elementwise import cast_time_major, transpose_bf16, cast_bf16
+from .head import head_forward, head_backward
 
 
 def supported(model, x):
-    return False
+    if not native.available():
+        return False
+    lstm = model.lstm
+    H, D = lstm.hidden_size, lstm.num_direction
+    cls = model.classifier
+    feat = model.num_comp * model.window_size
+    return (x.dim() == 4 and x.shape[0] <= 64 and lstm_supported(H, D) and model.input_size % 8 == 0
+            and feat % 8 == 0 and cls[1].in_features % 8 == 0 and cls[4].in_features % 2 == 0
+            and (not model.training or x.shape[0] > 1))
+
+
+def _w16(model, p):
+    sh = getattr(model, "_bf16_shadow", None)
+    if sh is not None and id(p) in sh:
+        return sh[id(p)]
+    return cast_bf16(p.detach())
+
+
+def _grad_buf(p):
+    if p.grad is None:
+        p.grad = torch.zeros_like(p)
+    return p.grad
+
+
+def _adjacent(a, b):
+    """True when ``b`` starts exactly where ``a`` ends inside the SAME storage (flat buffers)."""
+    return (a.untyped_storage().data_ptr() == b.untyped_storage().data_ptr()
+            and a.is_contiguous() and b.is_contiguous()
+            and a.data_ptr() + a.numel() * a.element_size() == b.data_ptr())
+
+
+def _span(a, shape, stride):
+    """View of ``shape`` starting at ``a`` and running on into the tensors that follow it."""
+    return torch.as_strided(a, shape, stride, storage_offset=a.storage_offset())
+
+
+class _ICALstmFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, model, *params):
+        lib = native.require_gpu()
+        B, S = x.shape[0], x.shape[1]
+        enc_l = model.encoder[0]
+        cells = list(model.lstm.lstms)
+        D, H = len(cells), model.lstm.hidden_size
+        E = model.input_size
+        cls = model.classifier
+        training = model.training
+
+        # 1. cast + time-major
+        xb, xT = cast_time_major(x.float(), want_transpose=True)
+        # 2. encoder: relu(x W^T + b), plus the transposed copy the i2h weight-gradient GEMM needs
+        BSp = (S * B + 7) // 8 * 8
+        encT = torch.empty(E, BSp, device=x.device, dtype=torch.bfloat16)[:, :S * B]
+        enc = gemm_bf16(xb, _w16(model, enc_l.weight), out_dtype=torch.bfloat16, bias_n=enc_l.bias.detach(),
+                        relu=True, out_t=encT)
+        # 3. input projection for every timestep, both directions
+        w_ih = [_w16(model, c.i2h.weight) for c in cells]
+        PX = torch.empty(S * B, D * 4 * H, device=x.device, dtype=torch.float32)
+        if D == 2 and _adjacent(w_ih[0], w_ih[1]) and _adjacent(cells[0].i2h.bias.detach(), cells[1].i2h.bias.detach()):
+            w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
+            b_cat = _span(cells[0].i2h.bias.detach(), (D * 4 * H,), (1,))
+            gemm_bf16(enc, w_cat, out=PX, bias_n=b_cat)
+        else:
+            for d in range(D):
+                gemm_bf16(enc, w_ih[d], out=PX[:, d * 4 * H:(d + 1) * 4 * H], bias_n=cells[d].i2h.bias.detach())
+        # 4. recurrence
+        whh = [_w16(model, c.h2h.weight) for c in cells]
+        bhh = [c.h2h.bias.detach() for c in cells]
+        Hmean, hT, cT, C, Hprev = lstm_forward(PX, whh, bhh, B, S, H, D)
+        # 5. head
+        N0 = cls[1].in_features
+        drop = None
+        p_drop = cls[0].p
+        if training and p_drop > 0:
+            drop = torch.empty(B, N0, device=x.device, dtype=torch.float32).bernoulli_(1 - p_drop).div_(1 - p_drop)
+        W1, W2, W3 = _w16(model, cls[1].weight), _w16(model, cls[4].weight), _w16(model, cls[6].weight)
+        bn = cls[2]
+        logits, head_saved = head_forward(Hmean, drop, W1, cls[1].bias.detach(), bn.weight.detach(), bn.bias.detach(),
+                                          bn.running_mean, bn.running_var, W2, cls[4].bias.detach(), W3,
+                                          cls[6].bias.detach(), training, float(bn.momentum or 0.1), float(bn.eps))
+        if training:
+            bn.num_batches_tracked += 1
+
+        ctx.model = model
+        ctx.dims = (B, S, E, H, D)
+        ctx.saved = (xT, enc, encT, PX, C, Hprev, whh, w_ih, head_saved)
+        ctx.mark_non_differentiable(hT, cT)
+        return logits, hT, cT
+
+    @staticmethod
+    def backward(ctx, dlogits, _dh, _dc):
+        lib = native.require_gpu()
+        model = ctx.model
+        B, S, E, H, D = ctx.dims
+        (xT, enc, encT, P, C, Hprev, whh, w_ih, head_saved) = ctx.saved
+        ctx.saved = None
+        enc_l = model.encoder[0]
+        cells = list(model.lstm.lstms)
+        cls = model.classifier
+        bn = cls[2]
+        dev = dlogits.device
+
+        # 6. head backward (accumulates into the parameter gradients)
+        grads = dict(dW1=_grad_buf(cls[1].weight), db1=_grad_buf(cls[1].bias), dbn_w=_grad_buf(bn.weight),
+                     dbn_b=_grad_buf(bn.bias), dW2=_grad_buf(cls[4].weight), db2=_grad_buf(cls[4].bias),
+                     dW3=_grad_buf(cls[6].weight), db3=_grad_buf(cls[6].bias))
+        dHmean = head_backward(dlogits, head_saved, grads, accumulate=True)
+
+        # 7. BPTT
+        db_ih = [_grad_buf(c.i2h.bias) for c in cells]
+        db_hh = [_grad_buf(c.h2h.bias) for c in cells]
+        dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True)
+
+        # 8. K-major operands for the weight-gradient GEMMs
+        dPT = transpose_bf16(dP)                    # [D*4H, S*B]
+        HprevT = transpose_bf16(Hprev)              # [D*H,  S*B]
+        # 9. recurrent weights
+        for dd, c in enumerate(cells):
+            gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H], out=_grad_buf(c.h2h.weight),
+                      accumulate=True, split_k=1)
+        # 10. input-projection weights
+        g_ih = [_grad_buf(c.i2h.weight) for c in cells]
+        if D == 2 and _adjacent(g_ih[0], g_ih[1]):
+            gemm_bf16(dPT, encT, out=_span(g_ih[0], (D * 4 * H, E), (E, 1)), accumulate=True)
+        else:
+            for dd in range(D):
+                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], encT, out=g_ih[dd], accumulate=True)
+        # 11. through the input projection and the encoder ReLU; bias gradient as column sums;
+        #     result stored transposed (K-major operand of the encoder weight gradient)
+        if D == 2 and _adjacent(w_ih[0], w_ih[1]):
+            w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
+        else:
+            w_cat = torch.cat(w_ih, 0)
+        w_ihT = transpose_bf16(w_cat)               # [E, D*4H]
+        BSp = (S * B + 7) // 8 * 8
+        d_encT = torch.empty(E, BSp, device=dev, dtype=torch.bfloat16)[:, :S * B]
+        gemm_bf16(dP, w_ihT, want_out=False, out_t=d_encT, mask=enc, colsum=_grad_buf(enc_l.bias))
+        # 12. encoder weights
+        gemm_bf16(d_encT, xT, out=_grad_buf(enc_l.weight), accumulate=True)
+        return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
 def icalstm_forward(model, x):
-    raise NotImplementedError
+    params = [p for p in model.parameters() if p.requires_grad]
+    logits, hT, cT = _ICALstmFn.apply(x, model, *params)
+    return logits, (hT, cT)

@@ -173,3 +173,61 @@ def reset_launch_count():
 
 def _p(t):
     return 0 if t is None else t.data_ptr()
+
+
+class LstmFwdDesc(ctypes.Structure):
+    _fields_ = [
+        ("PX", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2), ("bhh", ctypes.c_void_p * 2),
+        ("C", ctypes.c_void_p), ("Hprev", ctypes.c_void_p), ("Hmean", ctypes.c_void_p),
+        ("hT", ctypes.c_void_p), ("cT", ctypes.c_void_p),
+        ("B", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int), ("D", ctypes.c_int),
+    ]
+
+
+class LstmBwdDesc(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_void_p), ("C", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2),
+        ("dHmean", ctypes.c_void_p), ("dP", ctypes.c_void_p),
+        ("db_ih", ctypes.c_void_p * 2), ("db_hh", ctypes.c_void_p * 2),
+        ("accumulate", ctypes.c_int),
+        ("B", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int), ("D", ctypes.c_int),
+    ]
+
+
+class HeadFwdDesc(ctypes.Structure):
+    _fields_ = [
+        ("x", ctypes.c_void_p), ("drop", ctypes.c_void_p),
+        ("W1", ctypes.c_void_p), ("W2", ctypes.c_void_p), ("W3", ctypes.c_void_p),
+        ("b1", ctypes.c_void_p), ("b2", ctypes.c_void_p), ("b3", ctypes.c_void_p),
+        ("bn_w", ctypes.c_void_p), ("bn_b", ctypes.c_void_p),
+        ("run_mean", ctypes.c_void_p), ("run_var", ctypes.c_void_p),
+        ("momentum", ctypes.c_float), ("eps", ctypes.c_float), ("training", ctypes.c_int),
+        ("a0", ctypes.c_void_p),
+        ("xhat", ctypes.c_void_p), ("invstd", ctypes.c_void_p), ("a1", ctypes.c_void_p), ("a2", ctypes.c_void_p),
+        ("logits", ctypes.c_void_p),
+        ("B", ctypes.c_int), ("N0", ctypes.c_int), ("N1", ctypes.c_int), ("N2", ctypes.c_int), ("N3", ctypes.c_int),
+    ]
+
+
+class HeadBwdDesc(ctypes.Structure):
+    _fields_ = [
+        ("dlogits", ctypes.c_void_p),
+        ("a0", ctypes.c_void_p), ("drop", ctypes.c_void_p), ("xhat", ctypes.c_void_p), ("invstd", ctypes.c_void_p),
+        ("a1", ctypes.c_void_p), ("a2", ctypes.c_void_p),
+        ("W1", ctypes.c_void_p), ("W2", ctypes.c_void_p), ("W3", ctypes.c_void_p),
+        ("bn_w", ctypes.c_void_p),
+        ("dW1", ctypes.c_void_p), ("db1", ctypes.c_void_p), ("dbn_w", ctypes.c_void_p), ("dbn_b", ctypes.c_void_p),
+        ("dW2", ctypes.c_void_p), ("db2", ctypes.c_void_p), ("dW3", ctypes.c_void_p), ("db3", ctypes.c_void_p),
+        ("dx", ctypes.c_void_p),
+        ("training", ctypes.c_int), ("accumulate", ctypes.c_int),
+        ("B", ctypes.c_int), ("N0", ctypes.c_int), ("N1", ctypes.c_int), ("N2", ctypes.c_int), ("N3", ctypes.c_int),
+    ]
+
+
+def vp(t):
+    """c_void_p of a tensor's storage (None -> NULL)."""
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def ll(v):
+    return ctypes.c_longlong(int(v))

@@ -93,6 +93,79 @@ typedef struct DnbGemmDesc {
 } DnbGemmDesc;
 int dnb_gemm_bf16(const DnbGemmDesc* desc, void* stream);
 
+/* ---- K5b/K5c: persistent bidirectional LSTM recurrence, forward and BPTT -----------------
+ * Reference cell: comps/icalstm/models.py:20-45 (double sigmoid on i/f/o, gate order i|f|o|g),
+ * bidirectional wrapper :59-66 (reverse direction on flipped time, outputs not flipped back).
+ * Rows of all [S*B, .] tensors are time-major: row = time * B + b.  H = per-direction hidden
+ * size, multiple of 32, <= 256.  D = 1 or 2 directions. */
+typedef struct DnbLstmFwdDesc {
+    float* PX;               /* [S*B, D*4H] in: i2h(x)+b_ih for every timestep; out: full pre-activations */
+    const void* Whh[2];      /* per direction [4H, H] bf16, 16-byte aligned */
+    const float* bhh[2];     /* per direction [4H] */
+    float* C;                /* [D, S, B, H] cell states per processing step (saved for backward) */
+    void* Hprev;             /* [S*B, D*H] bf16: h_{t-1} stored at the time row of step t */
+    float* Hmean;            /* [B, D*H] mean over time of h (reference models.py:109) */
+    float* hT; float* cT;    /* [B, D*H] final states (may be NULL) */
+    int B, S, H, D;
+} DnbLstmFwdDesc;
+int dnb_lstm_forward(const DnbLstmFwdDesc* desc, void* stream);
+
+typedef struct DnbLstmBwdDesc {
+    const float* P;          /* [S*B, D*4H] pre-activations from the forward */
+    const float* C;          /* [D, S, B, H] */
+    const void* Whh[2];
+    const float* dHmean;     /* [B, D*H] gradient w.r.t. Hmean */
+    void* dP;                /* [S*B, D*4H] bf16 out: gradient w.r.t. the pre-activations */
+    float* db_ih[2];         /* per direction [4H] bias gradient (required) */
+    float* db_hh[2];         /* same values, second bias (may be NULL) */
+    int accumulate;          /* add to the bias gradients instead of overwriting */
+    int B, S, H, D;
+} DnbLstmBwdDesc;
+int dnb_lstm_backward(const DnbLstmBwdDesc* desc, void* stream);
+
+/* ---- layout / cast helpers ---------------------------------------------------------------- */
+/* x fp32 [B,S,F] -> rows bf16 [S*B, ldr] (row = t*B + b) and, if colsT != NULL, its transpose
+ * colsT bf16 [F, ldt].  Replaces the per-sample Python encoder loop (reference
+ * comps/icalstm/models.py:107) with one time-major matrix for the encoder GEMM. */
+int dnb_cast_time_major(const float* x, void* rows, long long ldr, void* colsT, long long ldt, int B, int S, int F,
+                        void* stream);
+int dnb_transpose_bf16(const void* in, long long ldi, void* out, long long ldo, int R, int C, void* stream);
+int dnb_cast_f32_bf16(const float* in, void* out, long long n, void* stream);
+/* K10: [N,C,T] -> [N,S,C,W] windows (reference comps/icalstm/__init__.py:28-32) */
+int dnb_window_gather(const float* in, float* out, int N, int C, int T, int S, int W, int stride, void* stream);
+/* K6: softmax + mean cross-entropy forward and gradient in one pass (reference
+ * comps/icalstm/__init__.py:60-61, comps/fs/__init__.py:54-55).  prob / dlogits / loss may be NULL;
+ * log_softmax_out != 0 writes log-probabilities into prob. */
+int dnb_softmax_ce(const float* logits, const long long* labels, float* prob, float* dlogits, float* loss, int B,
+                   int ncls, int log_softmax_out, void* stream);
+
+/* ---- K8: ICA-LSTM classifier head (reference comps/icalstm/models.py:95-103) --------------- */
+typedef struct DnbHeadFwdDesc {
+    const float* x;            /* [B,N0] time-mean of the LSTM outputs */
+    const float* drop;         /* [B,N0] dropout scale (0 or 1/(1-p)), NULL when not training */
+    const void *W1, *W2, *W3;  /* bf16 [N1,N0], [N2,N1], [N3,N2] */
+    const float *b1, *b2, *b3, *bn_w, *bn_b;
+    float *run_mean, *run_var; /* BatchNorm running statistics (updated in training, used in eval) */
+    float momentum, eps;
+    int training;
+    float* a0;                 /* [B,N0] dropped input (NULL: not saved) */
+    float *xhat, *invstd, *a1, *a2, *logits;   /* [B,N1], [N1], [B,N1], [B,N2], [B,N3] */
+    int B, N0, N1, N2, N3;
+} DnbHeadFwdDesc;
+int dnb_head_forward(const DnbHeadFwdDesc* desc, void* stream);
+
+typedef struct DnbHeadBwdDesc {
+    const float* dlogits;      /* [B,N3] */
+    const float *a0, *drop, *xhat, *invstd, *a1, *a2;
+    const void *W1, *W2, *W3;
+    const float* bn_w;
+    float *dW1, *db1, *dbn_w, *dbn_b, *dW2, *db2, *dW3, *db3;  /* parameter gradients (fp32) */
+    float* dx;                 /* [B,N0] gradient w.r.t. x */
+    int training, accumulate;
+    int B, N0, N1, N2, N3;
+} DnbHeadBwdDesc;
+int dnb_head_backward(const DnbHeadBwdDesc* desc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

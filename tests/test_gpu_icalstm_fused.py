@@ -1,0 +1,83 @@
+"""Whole fused ICA-LSTM (forward + backward into param.grad) vs the eager fp32 module."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(kw, seed=0):
+    from dinunet_implementations_b200.models import ICALstm
+    torch.manual_seed(seed)
+    ref = ICALstm(fused=False, **kw).cuda()
+    with torch.no_grad():        # kernels consume bf16 weights: give both the same (bf16-representable) values
+        for p in ref.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.to(torch.bfloat16).float())
+    fused = ICALstm(fused=True, **kw).cuda()
+    fused.load_state_dict(copy.deepcopy(ref.state_dict()))
+    return ref, fused
+
+
+@pytest.mark.parametrize("kw,B,S", [
+    (dict(input_size=256, hidden_size=384, num_comps=100, window_size=10, num_cls=2), 16, 98),
+    (dict(input_size=64, hidden_size=128, num_comps=12, window_size=6, num_cls=3), 7, 11),
+    (dict(input_size=32, hidden_size=64, num_comps=8, window_size=5, num_cls=2), 33, 5),
+])
+@pytest.mark.parametrize("mode", ["eval", "train"])
+def test_fused_icalstm_matches_eager(kw, B, S, mode):
+    ref, fused = _pair(kw)
+    for m in (ref, fused):
+        m.train(mode == "train")
+        m.classifier[0].p = 0.0          # dropout off: masks would differ between the two paths
+    x = torch.randn(B, S, kw["num_comps"], kw["window_size"], device="cuda")
+    y = torch.randint(0, kw["num_cls"], (B,), device="cuda")
+    lo_r, (h_r, c_r) = ref(x)
+    lo_f, (h_f, c_f) = fused(x)
+    torch.cuda.synchronize()
+    assert torch.allclose(lo_f, lo_r, atol=3e-2, rtol=3e-2), (lo_f - lo_r).abs().max()
+    assert torch.allclose(h_f, h_r, atol=3e-2) and torch.allclose(c_f, c_r, atol=6e-2)
+    torch.nn.functional.cross_entropy(lo_r, y).backward()
+    torch.nn.functional.cross_entropy(lo_f, y).backward()
+    torch.cuda.synchronize()
+    # The two paths differ by bf16 rounding of activations, which flips a few ReLU gates that sit
+    # at ~0; a flipped gate changes single entries of a gradient by O(1) of that entry.  Compare
+    # direction and norm instead of the max entry (the exact kernel math is pinned down by
+    # tests/test_gpu_head.py, tests/test_gpu_lstm.py and tests/test_gpu_gemm.py).
+    top = max(p.grad.abs().max().item() for p in ref.parameters())
+    for (n, pr), (_, pf) in zip(ref.named_parameters(), fused.named_parameters()):
+        assert pf.grad is not None, n
+        if pr.grad.abs().max().item() < 1e-4 * top:
+            continue                      # analytically ~0 (bias in front of BatchNorm): pure noise
+        cos = torch.nn.functional.cosine_similarity(pf.grad.flatten(), pr.grad.flatten(), dim=0).item()
+        rel = ((pf.grad - pr.grad).norm() / pr.grad.norm()).item()
+        assert cos > 0.98 and rel < 0.2, (n, cos, rel)
+    if mode == "train":    # BatchNorm running statistics advanced identically
+        assert torch.allclose(fused.classifier[2].running_mean, ref.classifier[2].running_mean, atol=1e-2)
+        assert torch.allclose(fused.classifier[2].running_var, ref.classifier[2].running_var, atol=1e-2)
+        assert int(fused.classifier[2].num_batches_tracked) == 1
+
+
+def test_fused_softmax_ce_and_helpers():
+    from dinunet_implementations_b200.ops.elementwise import softmax_cross_entropy, window_gather, transpose_bf16, cast_time_major
+    torch.manual_seed(0)
+    z = torch.randn(37, 5, device="cuda", requires_grad=True)
+    y = torch.randint(0, 5, (37,), device="cuda")
+    loss, prob = softmax_cross_entropy(z, y)
+    (loss * 2.0).backward()
+    z2 = z.detach().clone().requires_grad_(True)
+    l2 = torch.nn.functional.cross_entropy(z2, y)
+    (l2 * 2.0).backward()
+    assert torch.allclose(loss, l2, atol=1e-5) and torch.allclose(prob, torch.softmax(z2, 1), atol=1e-5)
+    assert torch.allclose(z.grad, z2.grad, atol=1e-6)
+    d = torch.randn(3, 7, 50, device="cuda")
+    w = window_gather(d, 4, 3, 40)
+    ref = torch.stack([d[:, :, j * 3:j * 3 + 4] for j in range(10)], 1)
+    assert torch.equal(w, ref)
+    t = torch.randn(45, 70, device="cuda").to(torch.bfloat16)
+    assert torch.equal(transpose_bf16(t), t.t())
+    x = torch.randn(4, 6, 3, 5, device="cuda")
+    rows, colsT = cast_time_major(x)
+    r = x.reshape(4, 6, 15).permute(1, 0, 2).reshape(24, 15).to(torch.bfloat16)
+    assert torch.equal(rows, r) and torch.equal(colsT, r.t())
