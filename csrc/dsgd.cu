@@ -44,21 +44,22 @@ struct DsgdArgs {
     int nranks, rank, mode, opt, use_flags;
     float lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, momentum;
     uint32_t epoch;
+    uint32_t* dev_state;   // optional {completed steps, blocks-done counter, lr bits}: makes the launch replayable
 };
 
-__device__ __forceinline__ void flag_barrier(const DsgdArgs& a, int phase) {
+__device__ __forceinline__ void flag_barrier(const DsgdArgs& a, int phase, uint32_t epoch) {
     // Every block pairs up with the same-index block on each peer.
     __syncthreads();
     if (threadIdx.x < a.nranks) {
         const int peer = threadIdx.x;
         const size_t slot = ((size_t)phase * kMaxBlocks + blockIdx.x) * kMaxRanks;
-        dnb::st_release_sys(a.flags[peer] + slot + a.rank, a.epoch);
+        dnb::st_release_sys(a.flags[peer] + slot + a.rank, epoch);
         const uint32_t* mine = a.flags[a.rank] + slot + peer;
         const long long t0 = clock64();
-        while ((int32_t)(dnb::ld_acquire_sys(mine) - a.epoch) < 0) {
+        while ((int32_t)(dnb::ld_acquire_sys(mine) - epoch) < 0) {
             if (clock64() - t0 > dnb::kSpinBudgetCycles) {
                 printf("dnb: dSGD flag barrier timed out (rank %d waits for %d, block %d, phase %d, epoch %u)\n",
-                       a.rank, peer, blockIdx.x, phase, a.epoch);
+                       a.rank, peer, blockIdx.x, phase, epoch);
                 __trap();
             }
         }
@@ -99,7 +100,19 @@ __device__ __forceinline__ void store8_f32(float* base, long long i, const float
 
 template <int WIRE>
 __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs a) {
-    if (a.use_flags) flag_barrier(a, 0);
+    // Step-dependent scalars come either from the launch arguments or — when the launch lives in a
+    // CUDA graph and is replayed unchanged — from a small device-resident state block.
+    uint32_t epoch = a.epoch;
+    float lr = a.lr, bc1 = a.bc1, bc2 = a.bc2;
+    uint32_t t_dev = 0;
+    if (a.dev_state) {
+        t_dev = *reinterpret_cast<volatile uint32_t*>(a.dev_state) + 1u;
+        epoch = a.epoch + t_dev;
+        lr = __uint_as_float(*reinterpret_cast<volatile uint32_t*>(a.dev_state + 2));
+        bc1 = 1.f - powf(a.beta1, (float)t_dev);
+        bc2 = sqrtf(1.f - powf(a.beta2, (float)t_dev));
+    }
+    if (a.use_flags) flag_barrier(a, 0, epoch);
 
     long long lo = 0, hi = a.n;
     if (a.mode == 0 && a.nranks > 1) {
@@ -139,9 +152,9 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
                 float gk = g[k] + a.wd * p[k];
                 m[k] = a.beta1 * m[k] + (1.f - a.beta1) * gk;
                 v[k] = a.beta2 * v[k] + (1.f - a.beta2) * gk * gk;
-                float mhat = m[k] / a.bc1;
-                float denom = sqrtf(v[k]) / a.bc2 + a.eps;   // bc2 = sqrt(1 - beta2^t), as torch.optim.Adam
-                p[k] -= a.lr * mhat / denom;
+                float mhat = m[k] / bc1;
+                float denom = sqrtf(v[k]) / bc2 + a.eps;   // bc2 = sqrt(1 - beta2^t), as torch.optim.Adam
+                p[k] -= lr * mhat / denom;
             }
             store8_f32(a.v, i, v);
         } else {
@@ -149,7 +162,7 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
             for (int k = 0; k < 8; ++k) {
                 float gk = g[k] + a.wd * p[k];
                 m[k] = a.momentum * m[k] + gk;
-                p[k] -= a.lr * (a.momentum != 0.f ? m[k] : gk);
+                p[k] -= lr * (a.momentum != 0.f ? m[k] : gk);
             }
         }
         store8_f32(a.m, i, m);
@@ -170,7 +183,20 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
             if (a.shadow[a.rank]) *reinterpret_cast<uint4*>(a.shadow[a.rank] + i) = sh;
         }
     }
-    if (a.use_flags) flag_barrier(a, 1);
+    if (a.use_flags) flag_barrier(a, 1, epoch);
+    if (a.dev_state) {
+        // the last CTA to finish publishes the new step count; every CTA read the old one at entry
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned prev = atomicAdd(a.dev_state + 1, 1u);
+            if (prev == gridDim.x - 1) {
+                a.dev_state[1] = 0u;
+                a.dev_state[0] = t_dev;
+                __threadfence();
+            }
+        }
+    }
 }
 
 }  // namespace
@@ -200,6 +226,7 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     a.bc1 = 1.f - powf(d->beta1, (float)d->step);
     a.bc2 = sqrtf(1.f - powf(d->beta2, (float)d->step));
     a.grad_scale = d->grad_scale; a.momentum = d->momentum; a.epoch = d->epoch;
+    a.dev_state = d->dev_state;
     if (a.use_flags)
         for (int r = 0; r < d->nranks; ++r) DNB_REQUIRE(a.flags[r] != nullptr, "flags[%d] is null", r);
 

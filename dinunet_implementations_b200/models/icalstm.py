@@ -89,6 +89,15 @@ class ICALstm(nn.Module):
             nn.Dropout(0.25), nn.Linear(self.hidden_size, 256), nn.BatchNorm1d(256), nn.ReLU(),
             nn.Linear(256, 64), nn.ReLU(), nn.Linear(64, self.num_cls))
 
+    def flat_param_order(self):
+        """Order used when the parameters are packed into one flat buffer: the two directions'
+        i2h weights (and biases) adjacent, so a single GEMM projects both directions."""
+        cells = list(self.lstm.lstms)
+        order = [self.encoder[0].weight] + [c.i2h.weight for c in cells] + [c.h2h.weight for c in cells]
+        order += [self.classifier[1].weight, self.classifier[4].weight, self.classifier[6].weight]
+        order += [c.i2h.bias for c in cells] + [c.h2h.bias for c in cells]
+        return order
+
     def forward_eager(self, x):
         B, S = x.shape[0], x.shape[1]
         e = self.encoder(x.reshape(B * S, -1)).view(B, S, -1)

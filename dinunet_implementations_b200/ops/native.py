@@ -138,6 +138,7 @@ class DsgdDesc(ctypes.Structure):
         ("weight_decay", ctypes.c_float), ("momentum", ctypes.c_float),
         ("grad_scale", ctypes.c_float),
         ("epoch", ctypes.c_uint32),
+        ("dev_state", ctypes.c_void_p),
     ]
 
 

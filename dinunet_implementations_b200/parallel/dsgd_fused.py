@@ -28,10 +28,33 @@ def wire_dtype_from_bits(precision_bits, prefer_bf16=True):
     return torch.float32
 
 
+ALIGN = 64   # every parameter starts on a 64-element boundary: 16-byte aligned in bf16 for TMA / vector loads
+
+
+def flat_layout(params):
+    """``(offsets, total)`` for a list of parameters laid out with ``ALIGN``-element alignment."""
+    offs, cur = [], 0
+    for p in params:
+        offs.append(cur)
+        cur += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+    return offs, cur
+
+
+def ordered_params(module: torch.nn.Module):
+    """Trainable parameters in the module's preferred flat order (``flat_param_order()`` if it
+    defines one — e.g. both directions' i2h weights adjacent so one GEMM covers them)."""
+    if hasattr(module, "flat_param_order"):
+        ps = [p for p in module.flat_param_order() if p.requires_grad]
+        seen = {id(p) for p in ps}
+        ps += [p for p in module.parameters() if p.requires_grad and id(p) not in seen]
+        return ps
+    return [p for p in module.parameters() if p.requires_grad]
+
+
 class FusedDSGD:
     def __init__(self, group: SiteGroup, numel: int, wire_dtype=torch.float32, lr=1e-3, betas=(0.9, 0.999), eps=1e-8,
                  weight_decay=0.0, optimizer="adam", momentum=0.0, shadow_bf16=False, mode="auto", loss_scale=1.0,
-                 name="dsgd"):
+                 name="dsgd", device_state=False):
         self.group = group
         self.numel = int(numel)
         self.n = (self.numel + 7) // 8 * 8
@@ -54,6 +77,12 @@ class FusedDSGD:
         self.v = [torch.zeros(self.n, device=dev) for _ in range(n_states)]
         self.out = None
         self.t = 0
+        # device-resident {steps done, scratch, lr bits, 0} per locally driven site: lets the launch be
+        # captured once in a CUDA graph and replayed (step count / barrier epoch advance on the device)
+        self.dev_state = None
+        if device_state:
+            self.dev_state = [torch.zeros(4, device=dev, dtype=torch.int32) for _ in range(n_states)]
+            self.set_lr(self.lr)
         self._descs = None
         self._grad_staging = None   # per-site fp32 grads when the wire is 16-bit
 
@@ -61,30 +90,45 @@ class FusedDSGD:
     def sites_here(self):
         return list(range(self.group.nsites)) if self.group.backend == "local" else [self.group.rank]
 
-    def bind(self, module: torch.nn.Module, site=None):
-        """Move ``module``'s parameters into this site's flat buffer (values preserved)."""
+    def set_lr(self, lr):
+        self.lr = float(lr)
+        if self.dev_state is not None:
+            bits = torch.tensor([self.lr], dtype=torch.float32).view(torch.int32)
+            for st in self.dev_state:
+                st[2:3].copy_(bits)
+
+    def bind(self, module: torch.nn.Module, site=None, params=None):
+        """Move ``module``'s parameters into this site's flat buffer (values preserved).
+
+        Each parameter starts on an ``ALIGN`` boundary; the gaps stay zero in every buffer.  If
+        the bf16 shadow exists, ``module._bf16_shadow`` maps ``id(param)`` to its bf16 view so the
+        tensor-core kernels read weights without a per-step cast."""
         site = self.group.rank if site is None else site
         flat_p, flat_g = self.params[site], self.grads[site]
-        ps = [p for p in module.parameters() if p.requires_grad]
-        total = sum(p.numel() for p in ps)
+        ps = params if params is not None else ordered_params(module)
+        offs, total = flat_layout(ps)
         if total != self.numel:
-            raise ValueError(f"module has {total} trainable values, FusedDSGD was sized for {self.numel}")
+            raise ValueError(f"module needs {total} flat elements, FusedDSGD was sized for {self.numel}")
         staging = None
         if self.wire_dtype != torch.float32:
             staging = torch.zeros(self.n, device=self.group.device)
             self._grad_staging = self._grad_staging or {}
             self._grad_staging[site] = staging
-        off = 0
+        shadow_map = {}
         with torch.no_grad():
-            for p in ps:
+            for p, off in zip(ps, offs):
                 n = p.numel()
                 flat_p[off:off + n].copy_(p.detach().reshape(-1))
                 p.data = flat_p[off:off + n].view_as(p)
                 gsrc = flat_g if staging is None else staging
                 p.grad = gsrc[off:off + n].view_as(p)
-                off += n
+                if self.shadow is not None:
+                    shadow_map[id(p)] = self.shadow[site][off:off + n].view_as(p)
         if self.shadow is not None:
             self.shadow[site].copy_(flat_p)
+            module._bf16_shadow = shadow_map
+            for m in module.modules():
+                m._bf16_shadow = shadow_map
         return ps
 
     def pack_grads(self, site=None):
@@ -114,6 +158,7 @@ class FusedDSGD:
         d.beta1, d.beta2, d.eps = self.betas[0], self.betas[1], self.eps
         d.weight_decay, d.momentum = self.weight_decay, self.momentum
         d.grad_scale = 1.0 / (g.nsites * self.loss_scale)
+        d.dev_state = self.dev_state[state_ix].data_ptr() if self.dev_state is not None else None
         return d
 
     def step(self, lr=None):
@@ -123,8 +168,16 @@ class FusedDSGD:
             self._descs = [self._desc(s, i) for i, s in enumerate(self.sites_here())]
         self.pack_grads()
         self.t += 1
-        epoch = self.group.next_epoch()
         st = native.stream()
+        if self.dev_state is not None:
+            # replayable launch: the kernel reads/advances the step itself; epoch base stays 0
+            if lr is not None and float(lr) != self.lr:
+                self.set_lr(lr)
+            for d in self._descs:
+                d.step, d.epoch, d.lr = 1, 0, self.lr
+                native.check(lib.dnb_dsgd_fused_step(ctypes.byref(d), st), "dnb_dsgd_fused_step")
+            return
+        epoch = self.group.next_epoch()
         for d in self._descs:
             d.step, d.epoch, d.lr = self.t, epoch, float(self.lr if lr is None else lr)
             native.check(lib.dnb_dsgd_fused_step(ctypes.byref(d), st), "dnb_dsgd_fused_step")

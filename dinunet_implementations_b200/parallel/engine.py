@@ -24,7 +24,7 @@ import torch
 
 from ..distrib import trainable_params
 from .comm import SiteGroup
-from .dsgd_fused import FusedDSGD, wire_dtype_from_bits
+from .dsgd_fused import FusedDSGD, wire_dtype_from_bits, flat_layout, ordered_params
 
 
 def init_distributed_from_env():
@@ -44,15 +44,22 @@ def init_distributed_from_env():
 
 
 class DeviceEngine:
+    """See module docstring.  ``use_graph=True`` captures the whole step (zero-grad, forward,
+    backward, fused aggregation) in one CUDA graph after ``graph_warmup`` eager steps; every later
+    step is a single graph launch.  Requires an ``iteration`` without host syncs (no ``.item()``),
+    otherwise the engine silently keeps stepping eagerly."""
+
     def __init__(self, trainer, group: SiteGroup | None = None, arena_bytes: int | None = None, site: int | None = None,
-                 shadow_bf16: bool = False):
+                 shadow_bf16: bool = True, use_graph: bool = False, graph_warmup: int = 3):
         self.trainer = trainer
         self.cache = trainer.cache
         self.device = trainer.device["gpu"]
         if self.device.type != "cuda":
             raise RuntimeError("DeviceEngine needs the trainer on a CUDA device (cache['gpus'] = [i])")
-        self.params = trainable_params(trainer.nn)
-        numel = sum(p.numel() for p in self.params)
+        self.params = []
+        for m in trainer.nn.values():
+            self.params += ordered_params(m)
+        numel = flat_layout(self.params)[1]
         wire = wire_dtype_from_bits(self.cache.get("precision_bits", "32"))
         need = numel * (4 + wire.itemsize + (2 if shadow_bf16 else 0)) + (1 << 20)
         if group is None:
@@ -66,29 +73,130 @@ class DeviceEngine:
         self.site = group.rank if site is None else site
         opt = str(self.cache.get("optimizer", "adam")).lower()
         self.fused = FusedDSGD(group, numel, wire_dtype=wire, lr=float(self.cache.get("learning_rate", 1e-3)),
-                               optimizer=opt, momentum=float(self.cache.get("momentum", 0.0)), shadow_bf16=shadow_bf16)
+                               optimizer=opt, momentum=float(self.cache.get("momentum", 0.0)), shadow_bf16=shadow_bf16,
+                               device_state=True)
         holder = torch.nn.ModuleList(list(trainer.nn.values()))
-        self.fused.bind(holder, site=self.site)
-        self.local_iterations = max(int(self.cache.get("local_iterations", 1)), 1)
+        self.fused.bind(holder, site=self.site, params=self.params)
         self.steps = 0
+        # CUDA graph state
+        self.use_graph = bool(use_graph)
+        self.graph_warmup = int(graph_warmup)
+        self._graph = None
+        self.kernels_per_step = None
+        self._static_in = None
+        self._static_out = None
+        # async pipeline state (train_step_async / drain)
+        self._copy_stream = None
+        self._staging = None
+        self._loss_ring = None
+        self._pending = []
 
     # ------------------------------------------------------------------ training
     def to_device(self, batch):
         return {k: (v.to(self.device, non_blocking=True) if isinstance(v, torch.Tensor) else v)
                 for k, v in batch.items()}
 
+    def _step_body(self, batch):
+        self.trainer.train_mode()
+        self.fused.zero_grad(site=self.site)
+        it = self.trainer.iteration(batch)
+        it["loss"].backward()
+        self.fused.step()
+        return it
+
+    def _capture(self, dev_batch):
+        self._static_in = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in dev_batch.items()}
+        try:
+            from ..ops import native
+            g = torch.cuda.CUDAGraph()
+            n0 = native.launch_count()
+            with torch.cuda.graph(g):
+                it = self._step_body(self._static_in)
+            self.kernels_per_step = native.launch_count() - n0     # our kernels inside one replay
+            self._graph, self._static_out = g, it
+        except Exception as e:   # host sync inside iteration(), unsupported op, ...
+            from ..utils import logger
+            logger.warn(f"CUDA graph capture failed ({type(e).__name__}: {e}); stepping eagerly", True)
+            torch.cuda.synchronize()
+            self.use_graph = False
+            self._graph = None
+            return False
+        return True
+
+    def _load_static(self, dev_batch):
+        for k, v in dev_batch.items():
+            if isinstance(v, torch.Tensor):
+                self._static_in[k].copy_(v, non_blocking=True)
+
     def train_step(self, batch, micro_batches=None):
-        """One optimiser step: ``local_iterations`` micro-batches, then the fused aggregation."""
+        """One optimiser step on ``batch`` (dict of host or device tensors): forward, backward,
+        cross-site aggregation, update.  Returns the trainer's ``iteration`` dict; with a captured
+        graph its tensors are static buffers that the next step overwrites."""
+        if micro_batches:
+            return self._accumulate_step(micro_batches)
+        dev_batch = self.to_device(batch)
+        self.steps += 1
+        if self.use_graph and self._graph is None and self.steps > self.graph_warmup:
+            if self._capture(dev_batch):
+                self._graph.replay()      # capture records but does not execute: run the captured step once
+                return self._static_out
+        if self._graph is not None:
+            self._load_static(dev_batch)
+            self._graph.replay()
+            return self._static_out
+        return self._step_body(dev_batch)
+
+    def _accumulate_step(self, micro_batches):
+        """``local_iterations`` > 1: accumulate the micro-batch gradients, then aggregate once."""
         self.trainer.train_mode()
         self.fused.zero_grad(site=self.site)
         its = []
-        for mb in (micro_batches or [batch]):
+        for mb in micro_batches:
             it = self.trainer.iteration(self.to_device(mb))
-            (it["loss"] / len(micro_batches or [batch])).backward()
+            (it["loss"] / len(micro_batches)).backward()
             its.append(it)
         self.fused.step()
         self.steps += 1
-        return its[-1] if len(its) == 1 else self.trainer.reduce_iteration(its) | {"loss": its[-1]["loss"]}
+        red = self.trainer.reduce_iteration(its)
+        red["loss"] = its[-1]["loss"]
+        return red
+
+    # ------------------------------------------------------------------ pipelined stepping
+    def train_step_async(self, host_batch):
+        """Pipelined variant for host-resident (pinned) batches: the H2D copy of this batch runs on
+        a copy stream while the previous step still computes, and the loss comes back through a
+        pinned ring without stalling the launch thread.  Call ``drain()`` to collect the losses."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._staging = [None, None]
+            self._loss_ring = torch.zeros(64, dtype=torch.float32).pin_memory()
+        slot = self.steps & 1
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self._copy_stream):
+            if self._staging[slot] is not None:
+                self._copy_stream.wait_event(self._staging[slot][2])     # the step that used this slot consumed it
+            dev = {k: (v.to(self.device, non_blocking=True) if isinstance(v, torch.Tensor) else v)
+                   for k, v in host_batch.items()}
+            ready = torch.cuda.Event()
+            ready.record(self._copy_stream)
+        cur.wait_event(ready)
+        it = self.train_step(dev)
+        consumed = torch.cuda.Event()
+        consumed.record(cur)
+        self._staging[slot] = (dev, ready, consumed)
+        ring_ix = len(self._pending) % self._loss_ring.numel()
+        self._loss_ring[ring_ix:ring_ix + 1].copy_(it["loss"].detach().reshape(1), non_blocking=True)
+        self._pending.append(ring_ix)
+        if len(self._pending) == self._loss_ring.numel():
+            return self.drain()
+        return None
+
+    def drain(self):
+        """Wait for the in-flight steps and return their losses (floats, in submission order)."""
+        torch.cuda.current_stream(self.device).synchronize()
+        out = [float(self._loss_ring[i]) for i in self._pending]
+        self._pending = []
+        return out
 
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, dataset, mode="validation"):

@@ -22,6 +22,7 @@ import torch.nn.functional as F
 from ..data import COINNDataset, COINNDataHandle
 from ..models import MSANNet
 from ..nn import COINNTrainer
+from ..ops.elementwise import softmax_cross_entropy
 
 
 def read_covariates(path, index_column=None):
@@ -92,8 +93,7 @@ class FreeSurferTrainer(COINNTrainer):
         inputs = batch["inputs"].to(dev, non_blocking=True).float()
         labels = batch["labels"].to(dev, non_blocking=True).long()
         indices = batch["ix"].to(dev, non_blocking=True).long() if "ix" in batch else None
-        out = F.log_softmax(self.nn["fs_net"](inputs), 1)
-        loss = F.nll_loss(out, labels)
+        loss, out = softmax_cross_entropy(self.nn["fs_net"](inputs), labels, log_softmax_out=True)
         predicted = out.argmax(1)
         score = self.new_metrics()
         score.add(predicted, labels)                         # hard predictions (reference :57-59)

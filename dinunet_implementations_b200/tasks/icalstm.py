@@ -21,6 +21,7 @@ import torch.nn.functional as F
 from ..data import COINNDataset, COINNDataHandle
 from ..models import ICALstm
 from ..nn import COINNTrainer
+from ..ops.elementwise import softmax_cross_entropy
 
 
 def window_view(data: np.ndarray, window_size: int, window_stride: int, temporal_size: int) -> np.ndarray:
@@ -76,8 +77,7 @@ class ICATrainer(COINNTrainer):
         inputs = batch["inputs"].to(dev, non_blocking=True).float()
         labels = batch["labels"].to(dev, non_blocking=True).long()
         out, _ = self.nn["net"](inputs)
-        prob = torch.softmax(out, 1)
-        loss = F.cross_entropy(out, labels)
+        loss, prob = softmax_cross_entropy(out, labels)       # K6: softmax + CE + gradient in one launch on CUDA
         score = self.new_metrics()
         score.add(prob[:, 1], labels)
         val = self.new_averages()

@@ -66,6 +66,10 @@ typedef struct DnbDsgdDesc {
     float lr, beta1, beta2, eps, weight_decay, momentum;
     float grad_scale;                   /* 1 / (nranks * loss_scale) */
     uint32_t epoch;                     /* strictly increasing per launch; barrier generation */
+    uint32_t* dev_state;                /* optional device words {steps done, scratch counter, lr as float bits, 0}:
+                                           when set, step / epoch (= epoch + steps done + 1) / lr are read on the
+                                           device and the step count is advanced by the kernel, so the identical
+                                           launch can be replayed from a CUDA graph */
 } DnbDsgdDesc;
 int dnb_dsgd_fused_step(const DnbDsgdDesc* desc, void* stream);
 

@@ -71,7 +71,8 @@ def test_bind_module_trains_like_torch_adam():
     ref = torch.nn.Sequential(torch.nn.Linear(20, 32), torch.nn.ReLU(), torch.nn.Linear(32, 3)).cuda()
     ref.load_state_dict(nets[0].state_dict())
     ropt = torch.optim.Adam(ref.parameters(), lr=1e-2)
-    numel = sum(p.numel() for p in ref.parameters())
+    from dinunet_implementations_b200.parallel.dsgd_fused import flat_layout, ordered_params
+    numel = flat_layout(ordered_params(ref))[1]
     g = SiteGroup.local(S, arena_bytes=1 << 20)
     f = FusedDSGD(g, numel, lr=1e-2)
     for s in range(S):
