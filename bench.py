@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--precision-bits", default="16", choices=["16", "32"], help="gradient wire format")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--eager", action="store_true", help="ours: eager model + fused aggregation only")
+    ap.add_argument("--no-graph", action="store_true", help="ours: fused kernels launched one by one (profiling)")
     return ap.parse_args()
 
 
@@ -216,7 +217,7 @@ def main():
     if args.impl == "ours":
         tr = make_ica_trainer(local_rank, batch_size=args.batch, precision_bits=args.precision_bits,
                               fused=not args.eager)
-        engine = DeviceEngine(tr, use_graph=not args.eager)
+        engine = DeviceEngine(tr, use_graph=not (args.eager or args.no_graph))
 
         def step(batch):
             return engine.train_step(batch)["loss"]

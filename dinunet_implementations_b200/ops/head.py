@@ -53,6 +53,8 @@ def head_backward(dlogits, saved, grads, accumulate=True):
     for k in ("dW1", "db1", "dbn_w", "dbn_b", "dW2", "db2", "dW3", "db3"):
         setattr(d, k, grads[k].data_ptr())
     d.dx = dx.data_ptr()
+    dz1 = torch.empty(B, N1, device=dlogits.device)
+    d.dz1 = dz1.data_ptr()
     d.training, d.accumulate = int(saved["training"]), int(accumulate)
     d.B, d.N0, d.N1, d.N2, d.N3 = B, N0, N1, N2, N3
     native.check(lib.dnb_head_backward(ctypes.byref(d), native.stream()), "dnb_head_backward")

@@ -219,7 +219,7 @@ class HeadBwdDesc(ctypes.Structure):
         ("bn_w", ctypes.c_void_p),
         ("dW1", ctypes.c_void_p), ("db1", ctypes.c_void_p), ("dbn_w", ctypes.c_void_p), ("dbn_b", ctypes.c_void_p),
         ("dW2", ctypes.c_void_p), ("db2", ctypes.c_void_p), ("dW3", ctypes.c_void_p), ("db3", ctypes.c_void_p),
-        ("dx", ctypes.c_void_p),
+        ("dx", ctypes.c_void_p), ("dz1", ctypes.c_void_p),
         ("training", ctypes.c_int), ("accumulate", ctypes.c_int),
         ("B", ctypes.c_int), ("N0", ctypes.c_int), ("N1", ctypes.c_int), ("N2", ctypes.c_int), ("N3", ctypes.c_int),
     ]

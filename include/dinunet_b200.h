@@ -165,6 +165,7 @@ typedef struct DnbHeadBwdDesc {
     const float* bn_w;
     float *dW1, *db1, *dbn_w, *dbn_b, *dW2, *db2, *dW3, *db3;  /* parameter gradients (fp32) */
     float* dx;                 /* [B,N0] gradient w.r.t. x */
+    float* dz1;                /* [B,N1] scratch handed from the first to the second backward launch */
     int training, accumulate;
     int B, N0, N1, N2, N3;
 } DnbHeadBwdDesc;
