@@ -248,6 +248,14 @@ __device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint4 v) {
                  "r"(v.w)
                  : "memory");
 }
+// Asynchronous 16-byte store into (possibly another CTA's) shared memory that also signals
+// `complete_tx(16)` on an mbarrier living in the destination CTA: data and notification travel
+// together, no fence or cluster barrier needed on either side (async proxy on both ends).
+__device__ __forceinline__ void st_async_v4(uint32_t remote_addr, uint4 v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+                 ::"r"(remote_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(remote_bar)
+                 : "memory");
+}
 __device__ __forceinline__ void st_cluster_u32(uint32_t addr, uint32_t v) {
     asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }

@@ -39,7 +39,7 @@ struct Epi {
 
 template <int BN>
 struct SmemLayout {
-    static constexpr int kStages = (BN <= 64) ? 6 : 4;
+    static constexpr int kStages = (BN <= 64) ? 6 : (BN <= 128 ? 4 : 3);
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
@@ -62,7 +62,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t* tmem_full = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
     const int lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN;
     const int m0 = blockIdx.y * BM;
@@ -95,7 +95,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // (elect.sync under warp-uniform control flow keeps descriptors in uniform registers)
+        if (dnb::elect_one()) {
             for (int i = 0; i < num_kt; ++i) {
                 const int s = i % STAGES;
                 const uint32_t ph = (i / STAGES) & 1;
@@ -110,7 +111,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        if (dnb::elect_one()) {
             constexpr uint32_t idesc = dnb::umma_idesc_bf16(BM, BN);
             for (int i = 0; i < num_kt; ++i) {
                 const int s = i % STAGES;
@@ -250,18 +251,40 @@ DNB_EXPORT int dnb_gemm_bf16(const DnbGemmDesc* g, void* stream_) {
     DNB_REQUIRE(g->M > 0 && g->N > 0 && g->K > 0, "dnb_gemm_bf16: empty problem %dx%dx%d", g->M, g->N, g->K);
     DNB_REQUIRE(g->A && g->B, "dnb_gemm_bf16: null operand");
     DNB_REQUIRE(g->out || g->outT || g->colsum, "dnb_gemm_bf16: no output requested");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int mt = (g->M + BM - 1) / BM;
+    const int total_kt = (g->K + BK - 1) / BK;
     int bn = g->block_n;
     if (bn == 0) {
-        // largest tile that still yields >= ~3/4 of a wave; small problems prefer more CTAs
-        const int mt = (g->M + BM - 1) / BM;
-        bn = 32;
-        for (int cand : {128, 64}) {
-            if ((long)mt * ((g->N + cand - 1) / cand) >= 110) { bn = cand; break; }
+        // pick the tile width that minimises (waves) x (per-tile time ~ fixed cost + BN-proportional work)
+        double best = 1e30;
+        for (int cand : {256, 128, 64, 32}) {
+            if (cand > 32 && g->N <= cand / 2) continue;          // mostly padding
+            const long tiles = (long)mt * ((g->N + cand - 1) / cand);
+            const long waves = (tiles + sms - 1) / sms;
+            const double cost = (double)waves * (6.0 + (double)total_kt * (0.35 + cand / 128.0 * 0.5) + cand / 64.0);
+            if (cost < best) { best = cost; bn = cand; }
         }
         if (g->N <= 16) bn = 16;
-        else if (g->N <= 32) bn = 32;
     }
-    int splits = g->split_k < 1 ? 1 : g->split_k;
+    int splits = g->split_k;
+    const bool can_split = g->out && !g->out_bf16 && !g->outT && !g->relu && !g->mask && !g->bias_n && !g->bias_m &&
+                           !g->colsum && g->accumulate;
+    if (splits == 0 || (splits == 1 && can_split && g->split_k_auto)) {
+        // auto: fill the machine when there are few output tiles and a long K loop (atomic accumulate)
+        splits = 1;
+        if (can_split) {
+            const long tiles = (long)mt * ((g->N + bn - 1) / bn);
+            if (tiles < sms) {
+                splits = (int)(sms / tiles);
+                if (splits > total_kt / 3) splits = total_kt / 3;
+                if (splits < 1) splits = 1;
+            }
+        }
+    }
+    if (splits < 1) splits = 1;
     if (splits > 1) {
         DNB_REQUIRE(g->out && !g->out_bf16 && !g->outT && !g->relu && !g->mask && !g->bias_n && !g->bias_m &&
                         !g->colsum,
@@ -285,7 +308,8 @@ DNB_EXPORT int dnb_gemm_bf16(const DnbGemmDesc* g, void* stream_) {
         case 32: return launch<32>(ta, tb, e, g->M, g->N, g->K, splits, st);
         case 64: return launch<64>(ta, tb, e, g->M, g->N, g->K, splits, st);
         case 128: return launch<128>(ta, tb, e, g->M, g->N, g->K, splits, st);
-        default: DNB_REQUIRE(false, "block_n must be 0 (auto), 16, 32, 64 or 128 (got %d)", bn);
+        case 256: return launch<256>(ta, tb, e, g->M, g->N, g->K, splits, st);
+        default: DNB_REQUIRE(false, "block_n must be 0 (auto), 16, 32, 64, 128 or 256 (got %d)", bn);
     }
     return 0;
 }

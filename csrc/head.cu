@@ -100,10 +100,21 @@ __global__ void __launch_bounds__(kL1Warps * 32) head_l1_kernel(const HeadFwdArg
     float* xs = sm;                                   // [B][N0] dropped input
     float* zs = xs + a.B * a.N0;                      // [warps][FPW][kMaxB] pre-BN values
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, B = a.B;
-    for (int i = tid; i < B * a.N0; i += blockDim.x) {
-        const float v = a.x[i] * (a.drop ? a.drop[i] : 1.f);
-        xs[i] = v;
-        if (a.a0 && blockIdx.x == 0) a.a0[i] = v;
+    {
+        // vectorised, unrolled staging: independent 16-byte loads in flight instead of a dependent chain
+        const int n4 = B * a.N0 / 4;
+        const float4* x4 = reinterpret_cast<const float4*>(a.x);
+        const float4* d4 = reinterpret_cast<const float4*>(a.drop);
+#pragma unroll 4
+        for (int i = tid; i < n4; i += kL1Warps * 32) {
+            float4 v = x4[i];
+            if (d4) {
+                const float4 d = d4[i];
+                v.x *= d.x; v.y *= d.y; v.z *= d.z; v.w *= d.w;
+            }
+            reinterpret_cast<float4*>(xs)[i] = v;
+            if (a.a0 && blockIdx.x == 0) reinterpret_cast<float4*>(a.a0)[i] = v;
+        }
     }
     __syncthreads();
     const int j0 = (blockIdx.x * kL1Warps + warp) * FPW;
@@ -161,8 +172,16 @@ __global__ void __launch_bounds__(kL23Threads) head_l23_kernel(const HeadFwdArgs
     extern __shared__ float sm[];
     float* s1 = sm;                       // [B][N1]
     float* s2 = s1 + a.B * a.N1;          // [B][N2]
+    float* s3 = s2 + a.B * a.N2;          // [N3][N2] last-layer weights
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, B = a.B;
-    for (int i = tid; i < B * a.N1; i += kL23Threads) s1[i] = a.a1[i];
+    {
+        const int n4 = B * a.N1 / 4;
+        const float4* src = reinterpret_cast<const float4*>(a.a1);
+#pragma unroll 4
+        for (int i = tid; i < n4; i += kL23Threads) reinterpret_cast<float4*>(s1)[i] = src[i];
+#pragma unroll 2
+        for (int i = tid; i < a.N3 * a.N2; i += kL23Threads) s3[i] = __bfloat162float(a.W3[i]);
+    }
     __syncthreads();
     for (int j0 = warp * FPW; j0 < a.N2; j0 += (kL23Threads / 32) * FPW) {
         const int nfeat = min(FPW, a.N2 - j0);
@@ -183,9 +202,10 @@ __global__ void __launch_bounds__(kL23Threads) head_l23_kernel(const HeadFwdArgs
     __syncthreads();
     for (int idx = tid; idx < B * a.N3; idx += kL23Threads) {
         const int b = idx / a.N3, c = idx % a.N3;
-        const __nv_bfloat16* w = a.W3 + (size_t)c * a.N2;
+        const float* w = s3 + c * a.N2;
         float acc = a.b3[c];
-        for (int k = 0; k < a.N2; ++k) acc += __bfloat162float(w[k]) * s2[b * a.N2 + k];
+#pragma unroll 8
+        for (int k = 0; k < a.N2; ++k) acc += w[k] * s2[b * a.N2 + k];
         a.logits[idx] = acc;
     }
 }
@@ -199,8 +219,11 @@ __global__ void __launch_bounds__(kB23Threads, 1) head_bwd_l23_kernel(const Head
     float* sdl = sm;                       // [B][N3]
     float* sa2 = sdl + B * N3;             // [B][N2]
     float* sdz2 = sa2 + B * N2;            // [B][N2]
+    float* sw3 = sdz2 + B * N2;            // [N3][N2]
     for (int i = tid; i < B * N3; i += kB23Threads) sdl[i] = a.dlogits[i];
+#pragma unroll 4
     for (int i = tid; i < B * N2; i += kB23Threads) sa2[i] = a.a2[i];
+    for (int i = tid; i < N3 * N2; i += kB23Threads) sw3[i] = __bfloat162float(a.W3[i]);
     __syncthreads();
     for (int idx = tid; idx < N3 * N2; idx += kB23Threads) {
         const int c = idx / N2, k = idx % N2;
@@ -216,7 +239,7 @@ __global__ void __launch_bounds__(kB23Threads, 1) head_bwd_l23_kernel(const Head
     for (int idx = tid; idx < B * N2; idx += kB23Threads) {
         const int b = idx / N2, k = idx % N2;
         float s = 0.f;
-        for (int c = 0; c < N3; ++c) s += sdl[b * N3 + c] * __bfloat162float(a.W3[c * N2 + k]);
+        for (int c = 0; c < N3; ++c) s += sdl[b * N3 + c] * sw3[c * N2 + k];
         sdz2[idx] = sa2[idx] > 0.f ? s : 0.f;
     }
     __syncthreads();
@@ -234,17 +257,29 @@ __global__ void __launch_bounds__(kB23Threads, 1) head_bwd_l23_kernel(const Head
             xh[b] = b < B ? a.xhat[b * N1 + j] : 0.f;
             da1[b] = 0.f;
         }
-        for (int k = 0; k < N2; ++k) {
-            const float w = __bfloat162float(a.W2[(size_t)k * N1 + j]);
-            float s = 0.f;
+        for (int k0 = 0; k0 < N2; k0 += 8) {
+            float w8[8], old8[8];
 #pragma unroll
-            for (int b = 0; b < BTT; ++b)
-                if (b < B) {
-                    const float dz = sdz2[b * N2 + k];
-                    s += dz * a1r[b];
-                    da1[b] += dz * w;
+            for (int kk = 0; kk < 8; ++kk) {              // 8 independent loads per trip
+                const int k = k0 + kk;
+                w8[kk] = k < N2 ? __bfloat162float(a.W2[(size_t)k * N1 + j]) : 0.f;
+                old8[kk] = (acc_mode && k < N2) ? a.dW2[(size_t)k * N1 + j] : 0.f;
+            }
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int k = k0 + kk;
+                if (k < N2) {
+                    float s = 0.f;
+#pragma unroll
+                    for (int b = 0; b < BTT; ++b)
+                        if (b < B) {
+                            const float dz = sdz2[b * N2 + k];
+                            s += dz * a1r[b];
+                            da1[b] += dz * w8[kk];
+                        }
+                    a.dW2[(size_t)k * N1 + j] = old8[kk] + s;
                 }
-            put(a.dW2 + (size_t)k * N1 + j, s, acc_mode);
+            }
         }
         float dgamma = 0.f, dbeta = 0.f;
 #pragma unroll
@@ -283,7 +318,12 @@ __global__ void __launch_bounds__(kB1Threads) head_bwd_l1_kernel(const HeadBwdAr
         float* a0s = sm;                        // [B][N0]
         float* dzt = a0s + B * N0;              // [kJTile][B]
         const int j0 = blockIdx.x * kJTile;
-        for (int i = tid; i < B * N0; i += kB1Threads) a0s[i] = a.a0[i];
+        {
+            const int n4 = B * N0 / 4;
+            const float4* src = reinterpret_cast<const float4*>(a.a0);
+#pragma unroll 4
+            for (int i = tid; i < n4; i += kB1Threads) reinterpret_cast<float4*>(a0s)[i] = src[i];
+        }
         for (int i = tid; i < kJTile * B; i += kB1Threads) {
             const int jj = i / B, b = i % B;
             dzt[i] = (j0 + jj < N1) ? a.dz1[b * N1 + j0 + jj] : 0.f;
@@ -298,15 +338,20 @@ __global__ void __launch_bounds__(kB1Threads) head_bwd_l1_kernel(const HeadBwdAr
 #pragma unroll
                 for (int jj = 0; jj < kJTile; ++jj) s[jj] += dzt[jj * B + b] * xv;
             }
+            float old[kJTile];
 #pragma unroll
             for (int jj = 0; jj < kJTile; ++jj)
-                if (j0 + jj < N1) put(a.dW1 + (size_t)(j0 + jj) * N0 + k, s[jj], a.accumulate);
+                old[jj] = (a.accumulate && j0 + jj < N1) ? a.dW1[(size_t)(j0 + jj) * N0 + k] : 0.f;
+#pragma unroll
+            for (int jj = 0; jj < kJTile; ++jj)
+                if (j0 + jj < N1) a.dW1[(size_t)(j0 + jj) * N0 + k] = old[jj] + s[jj];
         }
     } else {
         // dx[b][k] = drop * sum_j dz1[b][j] * W1[j][k] for 64 columns; 4 thread groups split j
         float* dzs = sm;                        // [N1][B]  (feature-major: one float4 run per feature)
         float* red = dzs + N1 * B;              // [4][kKTile][B]
         const int k0 = (blockIdx.x - n_jblocks) * kKTile;
+#pragma unroll 4
         for (int i = tid; i < N1 * B; i += kB1Threads) {
             const int b = i / N1, j = i % N1;   // coalesced read of dz1[b][j]
             dzs[j * B + b] = a.dz1[i];
@@ -320,11 +365,19 @@ __global__ void __launch_bounds__(kB1Threads) head_bwd_l1_kernel(const HeadBwdAr
 #pragma unroll
             for (int b = 0; b < BT; ++b) acc[b] = 0.f;
             if (k < N0) {
-                for (int j = jp * jper; j < min(N1, (jp + 1) * jper); ++j) {
-                    const float w = __bfloat162float(a.W1[(size_t)j * N0 + k]);
+                const int jend = min(N1, (jp + 1) * jper);
+                for (int j = jp * jper; j < jend; j += 8) {
+                    float w8[8];
 #pragma unroll
-                    for (int b = 0; b < BT; ++b)
-                        if (b0 + b < B) acc[b] += dzs[j * B + b0 + b] * w;
+                    for (int jj = 0; jj < 8; ++jj)           // 8 weight loads in flight per trip
+                        w8[jj] = (j + jj < jend) ? __bfloat162float(a.W1[(size_t)(j + jj) * N0 + k]) : 0.f;
+#pragma unroll
+                    for (int jj = 0; jj < 8; ++jj)
+                        if (j + jj < jend) {
+#pragma unroll
+                            for (int b = 0; b < BT; ++b)
+                                if (b0 + b < B) acc[b] += dzs[(j + jj) * B + b0 + b] * w8[jj];
+                        }
                 }
             }
 #pragma unroll
@@ -370,7 +423,7 @@ DNB_EXPORT int dnb_head_forward(const DnbHeadFwdDesc* d, void* stream_) {
         DNB_LAUNCH_CHECK();
     }
     {
-        const size_t smem = (size_t)d->B * (d->N1 + d->N2) * sizeof(float);
+        const size_t smem = ((size_t)d->B * (d->N1 + d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
         DNB_CUDA_CHECK(cudaFuncSetAttribute(head_l23_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         head_l23_kernel<<<1, kL23Threads, smem, st>>>(a);
         DNB_LAUNCH_CHECK();
@@ -395,7 +448,7 @@ DNB_EXPORT int dnb_head_backward(const DnbHeadBwdDesc* d, void* stream_) {
                     a.dW2 && a.db2 && a.dW3 && a.db3 && a.dx && a.dz1,
                 "head bwd: null buffer");
     {
-        const size_t smem = (size_t)d->B * (d->N3 + 2 * d->N2) * sizeof(float);
+        const size_t smem = ((size_t)d->B * (d->N3 + 2 * d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
         if (d->B <= 16) head_bwd_l23_kernel<16><<<1, kB23Threads, smem, st>>>(a);
         else if (d->B <= 32) head_bwd_l23_kernel<32><<<1, kB23Threads, smem, st>>>(a);
         else head_bwd_l23_kernel<64><<<1, kB23Threads, smem, st>>>(a);

@@ -48,6 +48,7 @@ struct FwdArgs {
     float* Hmean;                    // [B, D*H]
     float* hT;                       // [B, D*H]
     float* cT;                       // [B, D*H]
+    long long* dbg;                  // optional: clock64 stamps of one mid-sequence step (profiling aid)
     int B, S, H, D;
 };
 
@@ -59,6 +60,7 @@ struct BwdArgs {
     __nv_bfloat16* dP;               // [S*B, D*4H] bf16 out
     float* db_a[2];                  // bias gradients [4H] (i2h and h2h biases get the same values)
     float* db_b[2];
+    long long* dbg;
     int accumulate;
     int B, S, H, D;
 };
@@ -72,6 +74,16 @@ __device__ __forceinline__ uint32_t sw128_off(int rows_per_block, int row, int k
 
 __device__ __forceinline__ float dsig(float y) { return y * (1.f - y); }
 
+#define DNB_STAMP(i)                                                  \
+    do {                                                              \
+        if (stamp) a.dbg[(i)] = clock64();                            \
+    } while (0)
+
+// descriptor address-field increments (units of 16 bytes) of k-step `k` inside operands made of
+// 64-wide k-blocks: A blocks are 128 rows (16 KB) apart, B blocks NB rows (2 KB) apart
+__device__ __forceinline__ constexpr uint64_t koff_a(int k) { return (uint64_t)((k >> 2) * (128 * 128 / 16) + (k & 3) * 2); }
+__device__ __forceinline__ constexpr uint64_t koff_b(int k) { return (uint64_t)((k >> 2) * (NB * 128 / 16) + (k & 3) * 2); }
+
 // ------------------------------------------------------------------------------------ forward
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
@@ -83,14 +95,18 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     uint8_t* sH = smem + a_bytes;                    // two buffers
     float* sAct = reinterpret_cast<float*>(sH + 2 * h_bytes);   // [4][NB][U]
     uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sAct + 4 * NB * U);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+    uint64_t* hbar = mma_bar + 1;                    // [2]: "h_{t-1} has fully arrived in buffer p"
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(hbar + 2);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);     // provably warp-uniform for the compiler
     const int ncta = dnb::cluster_nctarank();
     const int cta = dnb::cluster_ctarank();
     const int cid = blockIdx.x / ncta;
     const int dir = cid % a.D, b0 = (cid / a.D) * NB;
-    const int ldp = a.D * 4 * H, ldh = a.D * H;
+    const size_t ldp = (size_t)a.D * 4 * H, ldh = (size_t)a.D * H;
+    const int nvalid = min(NB, a.B - b0);            // real batch rows in this tile
+    const uint32_t h_tx_bytes = (uint32_t)(NB * H * 2);
 
     // ---- one-time: weight slice -> swizzled smem, zero h_{-1}
     const __nv_bfloat16* W = a.Whh[dir];
@@ -112,7 +128,12 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     if (warp == 0) {
         if (lane == 0) {
             dnb::mbar_init(mma_bar, 1);
+            dnb::mbar_init(&hbar[0], 1);
+            dnb::mbar_init(&hbar[1], 1);
             dnb::fence_mbar_init();
+            // arm the first phase of both buffers: step 1 reads buffer 1, step 2 reads buffer 0
+            if (a.S > 1) dnb::mbar_expect_tx(&hbar[1], h_tx_bytes);
+            if (a.S > 2) dnb::mbar_expect_tx(&hbar[0], h_tx_bytes);
         }
         __syncwarp();
         dnb::tmem_alloc(tmem_slot, 32);
@@ -122,58 +143,107 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    dnb::cluster_sync_all();       // every CTA's buffers are initialised before anyone writes remotely
+    dnb::cluster_sync_all();       // every CTA's buffers and barriers exist before anyone writes remotely
 
     // epilogue-1 role: thread = gate row (q = warp, u = lane)
     const int grow = warp * H + cta * U + lane;
     const float bias = a.bhh[dir][grow];
     // epilogue-2 role: thread = (batch b2, 4 consecutive units)
     const int b2 = tid >> 3, ug = tid & 7;
-    const bool b2_ok = (b0 + b2) < a.B;
+    const bool b2_ok = b2 < nvalid;
     float c[4] = {0.f, 0.f, 0.f, 0.f}, hsum[4] = {0.f, 0.f, 0.f, 0.f}, hlast[4] = {0.f, 0.f, 0.f, 0.f};
 
-    // h_{-1} = 0 in the saved sequence
-    {
-        const int row0 = (dir ? a.S - 1 : 0) * a.B + b0 + b2;
-        if (b2_ok) *reinterpret_cast<uint2*>(a.Hprev + (size_t)row0 * ldh + dir * H + cta * U + ug * 4) = make_uint2(0, 0);
-    }
+    // pointers walk the sequence in processing order (reverse direction: time runs backwards)
+    const long long row_step = dir ? -(long long)a.B : (long long)a.B;
+    const long long row_first = (long long)(dir ? a.S - 1 : 0) * a.B + b0;
+    float* px_ptr = a.PX + (size_t)row_first * ldp + (size_t)dir * 4 * H + grow;          // + b*ldp
+    const long long px_step = row_step * (long long)ldp;
+    float* c_ptr = a.C + (((size_t)dir * a.S) * a.B + b0 + b2) * H + cta * U + ug * 4;     // step stride B*H
+    const size_t c_step = (size_t)a.B * H;
+    __nv_bfloat16* hp_ptr = a.Hprev + (size_t)(row_first + b2) * ldh + (size_t)dir * H + cta * U + ug * 4;
+    const long long hp_step = row_step * (long long)ldh;
+
+    if (b2_ok) *reinterpret_cast<uint2*>(hp_ptr) = make_uint2(0, 0);      // h_{-1} = 0 in the saved sequence
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
-    const uint32_t sA_addr = dnb::smem_u32(sA);
+    const uint64_t da_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sA));
+    const uint64_t db_base0 = dnb::umma_desc_k_sw128(dnb::smem_u32(sH));
+    const uint64_t db_base1 = dnb::umma_desc_k_sw128(dnb::smem_u32(sH + h_bytes));
+    const int ksteps = H / 16;
+    // destination of this thread's 16-byte h chunk (even ug lanes send): same offset in every CTA
+    const uint32_t chunk_off = sw128_off(NB, b2, cta * U + (ug & ~1) * 4);
+    const uint32_t send_data[2] = {dnb::smem_u32(sH) + chunk_off, dnb::smem_u32(sH + h_bytes) + chunk_off};
+    const uint32_t send_bar[2] = {dnb::smem_u32(&hbar[0]), dnb::smem_u32(&hbar[1])};
+
+    // Software pipeline: i2h(x) for step t+1 is fetched during step t; the global stores of step t
+    // (saved pre-activations, cell state, h for the weight-gradient GEMM) are issued at the start of
+    // step t+1 while the MMA runs.  Cross-CTA hand-off of h_t is st.async + mbarrier complete_tx:
+    // no fences, no cluster barrier on the critical path.
+    float px_next[NB];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) px_next[b] = (b < nvalid) ? px_ptr[(size_t)b * ldp] : 0.f;
+    float pst[NB];
+    uint2 hb_prev = make_uint2(0, 0);
 
     for (int t = 0; t < a.S; ++t) {
-        const int trow = (dir ? a.S - 1 - t : t) * a.B + b0;
-        // i2h(x_t) for this thread's gate row, all 16 batch entries (coalesced across the warp)
+        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t == a.S / 2;
+        DNB_STAMP(0);
         float px[NB];
 #pragma unroll
-        for (int b = 0; b < NB; ++b)
-            px[b] = (b0 + b < a.B) ? a.PX[(size_t)(trow + b) * ldp + dir * 4 * H + grow] : 0.f;
+        for (int b = 0; b < NB; ++b) px[b] = px_next[b];
 
-        if (tid == 0) {
-            dnb::fence_proxy_async();
+        if (warp == 0) {
+            // Warp-uniform control flow + elect.sync: the descriptors stay in uniform registers and
+            // each tcgen05.mma is a single UTCHMMA (a divergent `tid == 0` branch makes ptxas wrap
+            // every MMA in a lane-election loop, ~60 cycles apiece).
+            if (t > 0) dnb::mbar_wait_cluster(&hbar[t & 1], ((t - 1) >> 1) & 1);   // h_{t-1} complete
             dnb::tc_fence_after();
-            const uint32_t sB_addr = dnb::smem_u32(sH + (t & 1) * h_bytes);
-            for (int k = 0; k < H / 16; ++k) {
-                const uint64_t da = dnb::umma_desc_k_sw128(sA_addr + (k >> 2) * (128 * 128)) + 2 * (k & 3);
-                const uint64_t db = dnb::umma_desc_k_sw128(sB_addr + (k >> 2) * (NB * 128)) + 2 * (k & 3);
-                dnb::umma_bf16_ss(tmem_base, da, db, idesc, k != 0);
+            const uint64_t db_base = (t & 1) ? db_base1 : db_base0;
+            if (dnb::elect_one()) {
+                if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if (k < ksteps) dnb::umma_bf16_ss(tmem_base, da_base + koff_a(k), db_base + koff_b(k), idesc, k != 0);
+                dnb::umma_commit(mma_bar);
             }
-            dnb::umma_commit(mma_bar);
+            __syncwarp();
         }
+        DNB_STAMP(1);
+        // ---- while the MMA runs: deferred stores of step t-1, prefetch of step t+1
+        if (t > 0) {
+            float* pprev = px_ptr - px_step;
+#pragma unroll
+            for (int b = 0; b < NB; ++b)
+                if (b < nvalid) pprev[(size_t)b * ldp] = pst[b];
+            if (b2_ok) {
+                *reinterpret_cast<float4*>(c_ptr - c_step) = make_float4(c[0], c[1], c[2], c[3]);
+                *reinterpret_cast<uint2*>(hp_ptr) = hb_prev;          // h_{t-1} at the time row of step t
+            }
+        }
+        if (t + 1 < a.S) {
+            const float* pn = px_ptr + px_step;
+#pragma unroll
+            for (int b = 0; b < NB; ++b) px_next[b] = (b < nvalid) ? pn[(size_t)b * ldp] : 0.f;
+        }
+        DNB_STAMP(2);
         dnb::mbar_wait(mma_bar, t & 1);
         dnb::tc_fence_after();
+        DNB_STAMP(3);
         uint32_t acc[NB];
         dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
         dnb::tmem_ld_wait();
+        DNB_STAMP(4);
 #pragma unroll
         for (int b = 0; b < NB; ++b) {
             const float p = __uint_as_float(acc[b]) + px[b] + bias;
-            if (b0 + b < a.B) a.PX[(size_t)(trow + b) * ldp + dir * 4 * H + grow] = p;   // saved for BPTT
+            pst[b] = p;                                           // saved for BPTT (stored next step)
             const float act = (warp < 3) ? dnb::sigmoid_fast(dnb::sigmoid_fast(p)) : dnb::tanh_fast(p);
             sAct[(warp * NB + b) * U + lane] = act;
         }
+        DNB_STAMP(5);
         dnb::tc_fence_before();
         __syncthreads();
+        DNB_STAMP(6);
 
         // cell update: (b2, units ug*4 .. ug*4+3)
         const float4 gi = *reinterpret_cast<const float4*>(sAct + (0 * NB + b2) * U + ug * 4);
@@ -188,31 +258,39 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             hlast[j] = ov[j] * dnb::tanh_fast(c[j]);
             hsum[j] += hlast[j];
         }
-        if (b2_ok)
-            *reinterpret_cast<float4*>(a.C + (((size_t)dir * a.S + t) * a.B + b0 + b2) * H + cta * U + ug * 4) =
-                make_float4(c[0], c[1], c[2], c[3]);
         uint2 hb;
         hb.x = dnb::pack_bf16x2(hlast[0], hlast[1]);
         hb.y = dnb::pack_bf16x2(hlast[2], hlast[3]);
+        hb_prev = hb;
         if (t + 1 < a.S) {
-            if (b2_ok) {
-                const int nrow = (dir ? a.S - 2 - t : t + 1) * a.B + b0 + b2;
-                *reinterpret_cast<uint2*>(a.Hprev + (size_t)nrow * ldh + dir * H + cta * U + ug * 4) = hb;
-            }
-            // pair two lanes into one 16-byte swizzle chunk and push it into every CTA's next B operand
+            // pair two lanes into one 16-byte swizzle chunk; st.async drops it into every CTA's next
+            // B operand and counts 16 bytes on that CTA's "h arrived" barrier
             uint2 other;
             other.x = __shfl_xor_sync(0xffffffffu, hb.x, 1);
             other.y = __shfl_xor_sync(0xffffffffu, hb.y, 1);
             if ((ug & 1) == 0) {
                 const uint4 chunk = make_uint4(hb.x, hb.y, other.x, other.y);
-                const int k = cta * U + ug * 4;
-                const uint32_t off = dnb::smem_u32(sH + ((t + 1) & 1) * h_bytes) + sw128_off(NB, b2, k);
-                for (int peer = 0; peer < ncta; ++peer) dnb::st_cluster_v4(dnb::mapa(off, peer), chunk);
+                const uint32_t d_off = send_data[(t + 1) & 1], b_off = send_bar[(t + 1) & 1];
+                for (int peer = 0; peer < ncta; ++peer)
+                    dnb::st_async_v4(dnb::mapa(d_off, peer), chunk, dnb::mapa(b_off, peer));
             }
         }
-        dnb::fence_proxy_async();
-        dnb::cluster_arrive();
-        dnb::cluster_wait();
+        DNB_STAMP(7);
+        px_ptr += px_step;
+        c_ptr += c_step;
+        hp_ptr += hp_step;
+        // No block barrier here: sAct is rewritten only after the next MMA completes, and that MMA
+        // is issued only after every thread of this CTA has sent its h chunk (i.e. finished reading).
+        DNB_STAMP(8);
+        DNB_STAMP(9);
+    }
+    // flush the deferred stores of the last step
+    {
+        float* pprev = px_ptr - px_step;
+#pragma unroll
+        for (int b = 0; b < NB; ++b)
+            if (b < nvalid) pprev[(size_t)b * ldp] = pst[b];
+        if (b2_ok) *reinterpret_cast<float4*>(c_ptr - c_step) = make_float4(c[0], c[1], c[2], c[3]);
     }
 
     if (b2_ok) {
@@ -228,6 +306,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         dnb::tc_fence_after();
         dnb::tmem_dealloc(tmem_base, 32);
     }
+    dnb::cluster_sync_all();       // nobody leaves while a peer may still address its shared memory
 }
 
 // ------------------------------------------------------------------------------------ backward
@@ -243,13 +322,18 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const int ncta = dnb::cluster_nctarank();
     float* sDb = sRed + 2 * ncta * U * NB;               // [128] bias-gradient reduction
     uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sDb + 128);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_bar + 1);
+    uint64_t* rbar = mma_bar + 1;                        // [2]: "all partial dh blocks of round n arrived"
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rbar + 2);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int cta = dnb::cluster_ctarank();
     const int cid = blockIdx.x / ncta;
     const int dir = cid % a.D, b0 = (cid / a.D) * NB;
-    const int ldp = a.D * 4 * H, ldh = a.D * H;
+    const size_t ldp = (size_t)a.D * 4 * H, ldh = (size_t)a.D * H;
+    const int nvalid = min(NB, a.B - b0);
+    const uint32_t red_tx_bytes = (uint32_t)(ncta * U * NB * 4);
+    const int rounds = a.S - 1;
 
     // ---- one-time: A[unit k', own gate row j] = W_hh[j, k']  (transposed while loading)
     for (int idx = tid; idx < MT * tile_bytes / 16; idx += kThreads)
@@ -269,7 +353,11 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     if (warp == 0) {
         if (lane == 0) {
             dnb::mbar_init(mma_bar, 1);
+            dnb::mbar_init(&rbar[0], 1);
+            dnb::mbar_init(&rbar[1], 1);
             dnb::fence_mbar_init();
+            if (rounds > 0) dnb::mbar_expect_tx(&rbar[0], red_tx_bytes);
+            if (rounds > 1) dnb::mbar_expect_tx(&rbar[1], red_tx_bytes);
         }
         __syncwarp();
         dnb::tmem_alloc(tmem_slot, 32);
@@ -282,7 +370,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     dnb::cluster_sync_all();
 
     const int b2 = tid >> 3, ug = tid & 7;
-    const bool b_ok = (b0 + b2) < a.B;
+    const bool b_ok = b2 < nvalid;
     const int ucol = cta * U + ug * 4;                  // first of this thread's 4 hidden units
     float dc[4] = {0.f, 0.f, 0.f, 0.f};
     float dh_out[4] = {0.f, 0.f, 0.f, 0.f};
@@ -298,79 +386,138 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         for (int j = 0; j < 4; ++j) dbacc[q][j] = 0.f;
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
-    const uint32_t sA_addr = dnb::smem_u32(sA), sB_addr = dnb::smem_u32(sB);
+    const uint64_t da_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sA));
+    const uint64_t db_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sB));
+    const uint64_t tile_off = (uint64_t)(tile_bytes / 16);
+    // where this warp's partial-dh blocks go: tile mt of warp w belongs to CTA mt*4 + w
+    const uint32_t red_local[2] = {dnb::smem_u32(sRed + ((size_t)cta * U + lane) * NB),
+                                   dnb::smem_u32(sRed + (size_t)ncta * U * NB + ((size_t)cta * U + lane) * NB)};
+    const uint32_t rbar_local[2] = {dnb::smem_u32(&rbar[0]), dnb::smem_u32(&rbar[1])};
+    const uint32_t sB_off[4] = {sw128_off(NB, b2, 0 * U + ug * 4), sw128_off(NB, b2, 1 * U + ug * 4),
+                                sw128_off(NB, b2, 2 * U + ug * 4), sw128_off(NB, b2, 3 * U + ug * 4)};
+
+    // pointers walk the sequence backwards in processing order
+    const long long row_step = dir ? (long long)a.B : -(long long)a.B;      // towards step t-1
+    const long long row_last = (long long)(dir ? 0 : a.S - 1) * a.B + b0 + b2;   // time row of step S-1
+    const float* p_ptr = a.P + (size_t)row_last * ldp + (size_t)dir * 4 * H + ucol;       // + q*H
+    const long long p_step = row_step * (long long)ldp;
+    __nv_bfloat16* dp_ptr = a.dP + (size_t)row_last * ldp + (size_t)dir * 4 * H + ucol;
+    const float* c_ptr = a.C + (((size_t)dir * a.S + a.S - 1) * a.B + b0 + b2) * H + ucol;
+    const size_t c_step = (size_t)a.B * H;
+
+    // Software pipeline (see forward): the saved state of step t-1 is fetched while step t is
+    // processed; dP_t goes to global memory one step late; the activation recompute (MUFU-heavy,
+    // independent of dh) overlaps the MMA and the DSMEM reduction.
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 pq_n[4], cc_n, cp_n;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pq_n[q] = b_ok ? *reinterpret_cast<const float4*>(p_ptr + q * H) : z4;
+    cc_n = b_ok ? *reinterpret_cast<const float4*>(c_ptr) : z4;
+    cp_n = (b_ok && a.S > 1) ? *reinterpret_cast<const float4*>(c_ptr - c_step) : z4;
+    uint2 dp_store[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) dp_store[q] = make_uint2(0, 0);
 
     for (int t = a.S - 1; t >= 0; --t) {
-        const int trow = (dir ? a.S - 1 - t : t) * a.B + b0 + b2;
-        // saved forward state of my 4 cells (independent of the recurrence -> issue loads first)
-        float4 pq[4], cc, cp;
+        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t == a.S / 2;
+        DNB_STAMP(0);
+        float4 pq[4], cc = cc_n, cp = cp_n;
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            pq[q] = b_ok ? *reinterpret_cast<const float4*>(a.P + (size_t)trow * ldp + dir * 4 * H + q * H + ucol)
-                         : make_float4(0.f, 0.f, 0.f, 0.f);
-        cc = b_ok ? *reinterpret_cast<const float4*>(a.C + (((size_t)dir * a.S + t) * a.B + b0 + b2) * H + ucol)
-                  : make_float4(0.f, 0.f, 0.f, 0.f);
-        cp = (b_ok && t > 0)
-                 ? *reinterpret_cast<const float4*>(a.C + (((size_t)dir * a.S + t - 1) * a.B + b0 + b2) * H + ucol)
-                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < 4; ++q) pq[q] = pq_n[q];
 
-        float dh[4] = {dh_out[0], dh_out[1], dh_out[2], dh_out[3]};
-        if (t < a.S - 1) {
-            const int n = a.S - 2 - t;                  // index of this MMA round
-            if (tid == 0) {
-                dnb::fence_proxy_async();
-                dnb::tc_fence_after();
-                for (int mt = 0; mt < MT; ++mt)
-                    for (int k = 0; k < 8; ++k) {
-                        const uint64_t da =
-                            dnb::umma_desc_k_sw128(sA_addr + mt * tile_bytes + (k >> 2) * (128 * 128)) + 2 * (k & 3);
-                        const uint64_t db = dnb::umma_desc_k_sw128(sB_addr + (k >> 2) * (NB * 128)) + 2 * (k & 3);
-                        dnb::umma_bf16_ss(tmem_base + mt * NB, da, db, idesc, k != 0);
+        const int n = a.S - 2 - t;                  // index of this MMA round (valid when t < S-1)
+        if (t < a.S - 1 && warp == 0) {
+            dnb::tc_fence_after();
+            if (dnb::elect_one()) {
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+                    if (mt < MT) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k)
+                            dnb::umma_bf16_ss(tmem_base + mt * NB, da_base + mt * tile_off + koff_a(k),
+                                              db_base + koff_b(k), idesc, k != 0);
                     }
                 dnb::umma_commit(mma_bar);
             }
-            dnb::mbar_wait(mma_bar, n & 1);
-            dnb::tc_fence_after();
-            float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB;
-            for (int mt = 0; mt < MT; ++mt) {
-                const int dest = mt * 4 + warp;         // CTA owning units [32*dest, 32*dest+32)
-                uint32_t v[NB];
-                dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v);
-                dnb::tmem_ld_wait();
-                if (dest < ncta) {
-                    const uint32_t local = dnb::smem_u32(red_par + ((size_t)cta * U + lane) * NB);
-                    const uint32_t remote = dnb::mapa(local, dest);
+            __syncwarp();
+        }
+        DNB_STAMP(1);
+        // ---- while the MMA runs
+        if (t < a.S - 1 && b_ok) {                   // dP of step t+1 -> global
+            __nv_bfloat16* dprev = dp_ptr - p_step;
 #pragma unroll
-                    for (int x = 0; x < NB; x += 4)
-                        dnb::st_cluster_v4(remote + x * 4, make_uint4(v[x], v[x + 1], v[x + 2], v[x + 3]));
-                }
-            }
-            dnb::tc_fence_before();
-            dnb::cluster_arrive();
-            dnb::cluster_wait();
-            for (int src = 0; src < ncta; ++src) {
+            for (int q = 0; q < 4; ++q) *reinterpret_cast<uint2*>(dprev + q * H) = dp_store[q];
+        }
+        if (t > 0) {
+            const float* pn = p_ptr + p_step;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dh[j] += red_par[((size_t)src * U + ug * 4 + j) * NB + b2];
-            }
+            for (int q = 0; q < 4; ++q) pq_n[q] = b_ok ? *reinterpret_cast<const float4*>(pn + q * H) : z4;
+            cc_n = b_ok ? *reinterpret_cast<const float4*>(c_ptr - c_step) : z4;
+            cp_n = (b_ok && t > 1) ? *reinterpret_cast<const float4*>(c_ptr - 2 * c_step) : z4;
         }
 
         const float pi[4] = {pq[0].x, pq[0].y, pq[0].z, pq[0].w}, pf[4] = {pq[1].x, pq[1].y, pq[1].z, pq[1].w};
         const float po[4] = {pq[2].x, pq[2].y, pq[2].z, pq[2].w}, pg[4] = {pq[3].x, pq[3].y, pq[3].z, pq[3].w};
         const float cv[4] = {cc.x, cc.y, cc.z, cc.w}, cpv[4] = {cp.x, cp.y, cp.z, cp.w};
-        float dp[4][4];
+        // local Jacobian factors of the cell (recomputed from the saved pre-activations)
+        float k_i[4], k_f[4], k_g[4], k_h[4], k_tc[4], k_fg[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const float si = dnb::sigmoid_fast(pi[j]), sf = dnb::sigmoid_fast(pf[j]), so = dnb::sigmoid_fast(po[j]);
             const float i = dnb::sigmoid_fast(si), f = dnb::sigmoid_fast(sf), o = dnb::sigmoid_fast(so);
             const float g = dnb::tanh_fast(pg[j]);
             const float tc = dnb::tanh_fast(cv[j]);
-            const float dct = dc[j] + dh[j] * o * (1.f - tc * tc);
-            const float d_o = dh[j] * tc;
-            dp[0][j] = dct * g * dsig(i) * dsig(si);
-            dp[1][j] = dct * cpv[j] * dsig(f) * dsig(sf);
-            dp[2][j] = d_o * dsig(o) * dsig(so);
-            dp[3][j] = dct * i * (1.f - g * g);
-            dc[j] = dct * f;
+            k_h[j] = o * (1.f - tc * tc);            // dh -> dc
+            k_tc[j] = tc * dsig(o) * dsig(so);       // dp_o = dh  * k_tc
+            k_i[j] = g * dsig(i) * dsig(si);         // dp_i = dct * k_i
+            k_f[j] = cpv[j] * dsig(f) * dsig(sf);    // dp_f = dct * k_f
+            k_g[j] = i * (1.f - g * g);              // dp_g = dct * k_g
+            k_fg[j] = f;                             // dc_{t-1} = dct * f
+        }
+
+        float dh[4] = {dh_out[0], dh_out[1], dh_out[2], dh_out[3]};
+        DNB_STAMP(2);
+        if (t < a.S - 1) {
+            dnb::mbar_wait(mma_bar, n & 1);
+            dnb::tc_fence_after();
+            DNB_STAMP(3);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+                if (mt < MT) {
+                    const int dest = mt * 4 + warp;         // CTA owning units [32*dest, 32*dest+32)
+                    uint32_t v[NB];
+                    dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v);
+                    dnb::tmem_ld_wait();
+                    if (dest < ncta) {
+                        const uint32_t remote = dnb::mapa(red_local[n & 1], dest);
+                        const uint32_t rb = dnb::mapa(rbar_local[n & 1], dest);
+#pragma unroll
+                        for (int x = 0; x < NB; x += 4)
+                            dnb::st_async_v4(remote + x * 4, make_uint4(v[x], v[x + 1], v[x + 2], v[x + 3]), rb);
+                    }
+                }
+            DNB_STAMP(4);
+            dnb::tc_fence_before();
+            dnb::mbar_wait_cluster(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
+            DNB_STAMP(5);
+            const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB + b2;
+#pragma unroll
+            for (int src = 0; src < kMaxCtas; ++src)       // constant offsets, independent loads
+                if (src < ncta) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dh[j] += red_par[(src * U + j) * NB];
+                }
+        }
+        DNB_STAMP(6);
+        float dp[4][4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float dct = dc[j] + dh[j] * k_h[j];
+            dp[0][j] = dct * k_i[j];
+            dp[1][j] = dct * k_f[j];
+            dp[2][j] = dh[j] * k_tc[j];
+            dp[3][j] = dct * k_g[j];
+            dc[j] = dct * k_fg[j];
             if (!b_ok) { dp[0][j] = dp[1][j] = dp[2][j] = dp[3][j] = 0.f; dc[j] = 0.f; }
         }
 #pragma unroll
@@ -378,14 +525,25 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             uint2 pk;
             pk.x = dnb::pack_bf16x2(dp[q][0], dp[q][1]);
             pk.y = dnb::pack_bf16x2(dp[q][2], dp[q][3]);
-            if (b_ok) *reinterpret_cast<uint2*>(a.dP + (size_t)trow * ldp + dir * 4 * H + q * H + ucol) = pk;
-            // local B operand for the next (earlier) step: k = q*32 + ug*4 + j
-            *reinterpret_cast<uint2*>(sB + sw128_off(NB, b2, q * U + ug * 4)) = pk;
+            dp_store[q] = pk;
+            *reinterpret_cast<uint2*>(sB + sB_off[q]) = pk;      // local B operand of the next (earlier) step
 #pragma unroll
             for (int j = 0; j < 4; ++j) dbacc[q][j] += dp[q][j];
         }
-        dnb::fence_proxy_async();
+        DNB_STAMP(7);
+        p_ptr += p_step;
+        dp_ptr += p_step;
+        c_ptr -= c_step;
+        dnb::fence_proxy_async_smem();               // generic-proxy writes of sB -> visible to the MMA
+        DNB_STAMP(8);
         __syncthreads();
+        if (tid == 0 && t < a.S - 1 && n + 2 < rounds) dnb::mbar_expect_tx(&rbar[n & 1], red_tx_bytes);   // re-arm
+        DNB_STAMP(9);
+    }
+    if (b_ok) {                                      // dP of step 0
+        __nv_bfloat16* dprev = dp_ptr - p_step;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) *reinterpret_cast<uint2*>(dprev + q * H) = dp_store[q];
     }
 
     // bias gradients: sum over batch (threads sharing ug) — once per kernel
@@ -457,12 +615,13 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
         a.bhh[i] = d->bhh[i];
     }
     a.C = d->C; a.Hprev = reinterpret_cast<__nv_bfloat16*>(d->Hprev); a.Hmean = d->Hmean; a.hT = d->hT; a.cT = d->cT;
+    a.dbg = d->dbg;
     a.B = d->B; a.S = d->S; a.H = d->H; a.D = d->D;
     for (int i = 0; i < d->D; ++i)
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
     const int ncta = d->H / U, KB = (d->H + 63) / 64;
-    const size_t smem = (size_t)KB * 128 * 128 + 2 * (size_t)KB * NB * 128 + 4 * NB * U * 4 + 64 + 1024;
+    const size_t smem = (size_t)KB * 128 * 128 + 2 * (size_t)KB * NB * 128 + 4 * NB * U * 4 + 128 + 1024;
     const int tiles = (d->B + NB - 1) / NB;
     return launch_cluster(lstm_fwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }
@@ -479,6 +638,7 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
         a.db_b[i] = d->db_hh[i];
     }
     a.accumulate = d->accumulate;
+    a.dbg = d->dbg;
     a.B = d->B; a.S = d->S; a.H = d->H; a.D = d->D;
     for (int i = 0; i < d->D; ++i) DNB_REQUIRE(a.Whh[i] && a.db_a[i], "lstm bwd: W_hh/db[%d] missing", i);
     DNB_REQUIRE(a.P && a.C && a.dHmean && a.dP, "lstm bwd: null buffer");
@@ -491,6 +651,6 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
             if (a.db_b[i]) DNB_CUDA_CHECK(cudaMemsetAsync(a.db_b[i], 0, sizeof(float) * 4 * d->H, st));
         }
     }
-    const size_t smem = (size_t)MT * 2 * 128 * 128 + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + 64 + 1024;
+    const size_t smem = (size_t)MT * 2 * 128 * 128 + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + 128 + 1024;
     return launch_cluster(lstm_bwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }

@@ -33,7 +33,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None,
     if K != Kb:
         raise ValueError(f"K mismatch: a is {tuple(a.shape)}, b is {tuple(b.shape)}")
     if out is None and want_out:
-        out = (torch.zeros if (split_k > 1) else torch.empty)((M, N), device=a.device, dtype=out_dtype)
+        out = (torch.zeros if (split_k != 1) else torch.empty)((M, N), device=a.device, dtype=out_dtype)
     d = native.GemmDesc()
     d.A, d.lda, d.B, d.ldb = a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0)
     d.M, d.N, d.K = M, N, K

@@ -147,14 +147,14 @@ class _ICALstmFn(torch.autograd.Function):
         # 9. recurrent weights
         for dd, c in enumerate(cells):
             gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H], out=_grad_buf(c.h2h.weight),
-                      accumulate=True, split_k=1)
+                      accumulate=True, split_k=0)
         # 10. input-projection weights
         g_ih = [_grad_buf(c.i2h.weight) for c in cells]
         if D == 2 and _adjacent(g_ih[0], g_ih[1]):
-            gemm_bf16(dPT, encT, out=_span(g_ih[0], (D * 4 * H, E), (E, 1)), accumulate=True)
+            gemm_bf16(dPT, encT, out=_span(g_ih[0], (D * 4 * H, E), (E, 1)), accumulate=True, split_k=0)
         else:
             for dd in range(D):
-                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], encT, out=g_ih[dd], accumulate=True)
+                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], encT, out=g_ih[dd], accumulate=True, split_k=0)
         # 11. through the input projection and the encoder ReLU; bias gradient as column sums;
         #     result stored transposed (K-major operand of the encoder weight gradient)
         if D == 2 and _adjacent(w_ih[0], w_ih[1]):
@@ -166,7 +166,7 @@ class _ICALstmFn(torch.autograd.Function):
         d_encT = torch.empty(E, BSp, device=dev, dtype=torch.bfloat16)[:, :S * B]
         gemm_bf16(dP, w_ihT, want_out=False, out_t=d_encT, mask=enc, colsum=_grad_buf(enc_l.bias))
         # 12. encoder weights
-        gemm_bf16(d_encT, xT, out=_grad_buf(enc_l.weight), accumulate=True)
+        gemm_bf16(d_encT, xT, out=_grad_buf(enc_l.weight), accumulate=True, split_k=0)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 

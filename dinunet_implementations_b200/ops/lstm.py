@@ -12,7 +12,7 @@ def lstm_supported(H: int, D: int) -> bool:
     return H % 32 == 0 and 32 <= H <= 256 and D in (1, 2)
 
 
-def lstm_forward(px, whh, bhh, B, S, H, D):
+def lstm_forward(px, whh, bhh, B, S, H, D, dbg=None):
     """px ``[S*B, D*4H]`` fp32 (time-major rows, overwritten with the full pre-activations);
     whh: list of D bf16 ``[4H,H]``; bhh: list of D fp32 ``[4H]``.
     Returns ``(Hmean [B,D*H], hT, cT, C [D,S,B,H], Hprev bf16 [S*B, D*H])``."""
@@ -30,12 +30,13 @@ def lstm_forward(px, whh, bhh, B, S, H, D):
         assert bhh[i].dtype == torch.float32 and bhh[i].is_contiguous()
         d.Whh[i], d.bhh[i] = whh[i].data_ptr(), bhh[i].data_ptr()
     d.C, d.Hprev, d.Hmean, d.hT, d.cT = C.data_ptr(), Hprev.data_ptr(), Hmean.data_ptr(), hT.data_ptr(), cT.data_ptr()
+    d.dbg = dbg.data_ptr() if dbg is not None else None
     d.B, d.S, d.H, d.D = B, S, H, D
     native.check(lib.dnb_lstm_forward(ctypes.byref(d), native.stream()), "dnb_lstm_forward")
     return Hmean, hT, cT, C, Hprev
 
 
-def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=False):
+def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=False, dbg=None):
     """Returns ``dP`` bf16 ``[S*B, D*4H]``; bias gradients are written into ``db_ih`` / ``db_hh``
     (lists of D fp32 ``[4H]`` tensors)."""
     lib = native.require_gpu()
@@ -48,6 +49,7 @@ def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=F
         d.db_ih[i] = db_ih[i].data_ptr()
         d.db_hh[i] = db_hh[i].data_ptr() if db_hh is not None else None
     d.accumulate = int(accumulate)
+    d.dbg = dbg.data_ptr() if dbg is not None else None
     d.B, d.S, d.H, d.D = B, S, H, D
     native.check(lib.dnb_lstm_backward(ctypes.byref(d), native.stream()), "dnb_lstm_backward")
     return dP

@@ -155,6 +155,7 @@ class GemmDesc(ctypes.Structure):
         ("colsum", ctypes.c_void_p),
         ("alpha", ctypes.c_float),
         ("relu", ctypes.c_int), ("accumulate", ctypes.c_int), ("split_k", ctypes.c_int), ("block_n", ctypes.c_int),
+        ("split_k_auto", ctypes.c_int),
     ]
 
 
@@ -180,7 +181,7 @@ class LstmFwdDesc(ctypes.Structure):
     _fields_ = [
         ("PX", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2), ("bhh", ctypes.c_void_p * 2),
         ("C", ctypes.c_void_p), ("Hprev", ctypes.c_void_p), ("Hmean", ctypes.c_void_p),
-        ("hT", ctypes.c_void_p), ("cT", ctypes.c_void_p),
+        ("hT", ctypes.c_void_p), ("cT", ctypes.c_void_p), ("dbg", ctypes.c_void_p),
         ("B", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int), ("D", ctypes.c_int),
     ]
 
@@ -190,6 +191,7 @@ class LstmBwdDesc(ctypes.Structure):
         ("P", ctypes.c_void_p), ("C", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2),
         ("dHmean", ctypes.c_void_p), ("dP", ctypes.c_void_p),
         ("db_ih", ctypes.c_void_p * 2), ("db_hh", ctypes.c_void_p * 2),
+        ("dbg", ctypes.c_void_p),
         ("accumulate", ctypes.c_int),
         ("B", ctypes.c_int), ("S", ctypes.c_int), ("H", ctypes.c_int), ("D", ctypes.c_int),
     ]

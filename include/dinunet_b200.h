@@ -92,8 +92,10 @@ typedef struct DnbGemmDesc {
     float alpha;
     int relu;
     int accumulate;                     /* fp32 out += result (atomic) */
-    int split_k;                        /* >1: split the K loop over grid.z, needs plain fp32 out, pre-zeroed */
-    int block_n;                        /* 0 = auto, else 16/32/64/128 */
+    int split_k;                        /* >1: split the K loop over grid.z (plain fp32 out, atomically accumulated);
+                                           0: choose automatically when `accumulate` is set */
+    int block_n;                        /* 0 = auto, else 16/32/64/128/256 */
+    int split_k_auto;                   /* reserved (0) */
 } DnbGemmDesc;
 int dnb_gemm_bf16(const DnbGemmDesc* desc, void* stream);
 
@@ -110,6 +112,7 @@ typedef struct DnbLstmFwdDesc {
     void* Hprev;             /* [S*B, D*H] bf16: h_{t-1} stored at the time row of step t */
     float* Hmean;            /* [B, D*H] mean over time of h (reference models.py:109) */
     float* hT; float* cT;    /* [B, D*H] final states (may be NULL) */
+    long long* dbg;          /* optional: 16 clock64 stamps of one mid-sequence step (NULL normally) */
     int B, S, H, D;
 } DnbLstmFwdDesc;
 int dnb_lstm_forward(const DnbLstmFwdDesc* desc, void* stream);
@@ -122,6 +125,7 @@ typedef struct DnbLstmBwdDesc {
     void* dP;                /* [S*B, D*4H] bf16 out: gradient w.r.t. the pre-activations */
     float* db_ih[2];         /* per direction [4H] bias gradient (required) */
     float* db_hh[2];         /* same values, second bias (may be NULL) */
+    long long* dbg;          /* optional profiling stamps, as in the forward */
     int accumulate;          /* add to the bias gradients instead of overwriting */
     int B, S, H, D;
 } DnbLstmBwdDesc;

@@ -21,7 +21,7 @@ def _mk(M, N, K, seed=0):
 
 
 @pytest.mark.parametrize("M,N,K", SHAPES)
-@pytest.mark.parametrize("block_n", [0, 16, 32, 64, 128])
+@pytest.mark.parametrize("block_n", [0, 16, 32, 64, 128, 256])
 def test_gemm_plain(M, N, K, block_n):
     from dinunet_implementations_b200.ops.gemm import gemm_bf16
     a, b = _mk(M, N, K)
