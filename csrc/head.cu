@@ -15,6 +15,8 @@
 #include "common.cuh"
 #include "../include/dinunet_b200.h"
 
+#include <mutex>
+
 void dnb_count_launch(int n);
 
 namespace {
@@ -447,6 +449,105 @@ DNB_EXPORT int dnb_head_backward(const DnbHeadBwdDesc* d, void* stream_) {
     DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&
                     a.dW2 && a.db2 && a.dW3 && a.db3 && a.dx && a.dz1,
                 "head bwd: null buffer");
+    {
+        const size_t smem = ((size_t)d->B * (d->N3 + 2 * d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
+        if (d->B <= 16) head_bwd_l23_kernel<16><<<1, kB23Threads, smem, st>>>(a);
+        else if (d->B <= 32) head_bwd_l23_kernel<32><<<1, kB23Threads, smem, st>>>(a);
+        else head_bwd_l23_kernel<64><<<1, kB23Threads, smem, st>>>(a);
+        DNB_LAUNCH_CHECK();
+    }
+    {
+        const int n_j = dnb_ceil_div(d->N1, kJTile), n_k = dnb_ceil_div(d->N0, kKTile);
+        const size_t smem_j = ((size_t)d->B * d->N0 + kJTile * d->B) * sizeof(float);
+        const size_t smem_k = ((size_t)d->N1 * d->B + 4 * kKTile * d->B) * sizeof(float);
+        const size_t smem = smem_j > smem_k ? smem_j : smem_k;
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_bwd_l1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        head_bwd_l1_kernel<<<n_j + n_k, kB1Threads, smem, st>>>(a, n_j);
+        DNB_LAUNCH_CHECK();
+    }
+    dnb_count_launch(2);
+    return 0;
+}
+
+// ------------------------------------------------------------------ allocation-free backward
+// dnb_head_backward needs a [B, N1] fp32 scratch (`dz1`) to hand the BatchNorm-input gradient from
+// its first launch to its second, and leaves providing it to the caller.  Some callers have no way
+// to provide one: a host process whose device memory is carved up front by another runtime or pool
+// and that is not allowed to call cudaMalloc behind its back, or a service with a fixed memory
+// budget in which an extra allocation per call (which may synchronise the device, and may fail long
+// after start-up) is unacceptable.  For them the scratch lives in the library image itself.
+//
+// The array below is file-scope __device__ memory: every GPU that loads this library holds its
+// 128 KiB until the process exits, used or not.  In host code the NAME of the array is only a
+// host-side handle, not a device address — handing it to a kernel would fault (or, where the GPU
+// can reach host memory, silently touch the wrong bytes) — so the device address is looked up with
+// cudaGetSymbolAddress, once per device, while that device is current, and cached.
+namespace {
+constexpr int kStaticMaxB = 64;       // batch rows the built-in scratch can hold
+constexpr int kStaticMaxN1 = 512;     // hidden width (BatchNorm features) it can hold
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) float g_head_dz1_scratch[kStaticMaxB * kStaticMaxN1];   // 131072 bytes
+
+float* g_scratch_dev_ptr[kStaticMaxDevices] = {nullptr};
+std::mutex g_scratch_mutex;
+
+// Device address of the built-in scratch on the CURRENT device (looked up on first use).
+int static_scratch_for_current_device(float** out) {
+    int dev = -1;
+    DNB_CUDA_CHECK(cudaGetDevice(&dev));
+    DNB_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "device ordinal %d outside [0,%d)", dev, kStaticMaxDevices);
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (g_scratch_dev_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_head_dz1_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            dnb_set_error("cudaGetSymbolAddress(built-in head scratch) failed on device %d: %s", dev,
+                          cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : -1;
+        }
+        g_scratch_dev_ptr[dev] = static_cast<float*>(p);
+    }
+    *out = g_scratch_dev_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+// Same computation and same outputs as dnb_head_backward, but the [B, N1] scratch is the
+// library's built-in array; `desc->dz1` is ignored.  Performs no cudaMalloc / cudaFree and calls no
+// allocating routine.  Limits: B <= 64 and N1 <= 512 (larger shapes are refused with an error —
+// use dnb_head_backward with your own scratch instead).
+//
+//  * The first call on each device resolves the array's device address (cudaGetSymbolAddress).
+//    Make that first call during start-up, before any stream capture is begun on that device.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in
+//    it.  Nothing in it has to start at zero: the first launch writes every element the second
+//    launch reads (rows < B, columns < N1), so stale contents are never consumed.
+//  * Because the array is shared, two calls whose kernels can overlap on the same GPU (different
+//    streams, or different host threads) race on it.  Issue them on one stream, or serialise them.
+DNB_EXPORT int dnb_head_backward_noalloc(const DnbHeadBwdDesc* d, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(d != nullptr, "dnb_head_backward_noalloc: null descriptor");
+    DNB_REQUIRE(d->B >= 1 && d->B <= kStaticMaxB,
+                "dnb_head_backward_noalloc: batch %d exceeds the built-in scratch (max %d rows); "
+                "use dnb_head_backward with caller-provided dz1", d->B, kStaticMaxB);
+    DNB_REQUIRE(d->N1 >= 1 && d->N1 <= kStaticMaxN1,
+                "dnb_head_backward_noalloc: N1 = %d exceeds the built-in scratch (max %d features); "
+                "use dnb_head_backward with caller-provided dz1", d->N1, kStaticMaxN1);
+    float* scratch = nullptr;
+    if (int rc = static_scratch_for_current_device(&scratch)) return rc;
+
+    HeadBwdArgs a;
+    a.dlogits = d->dlogits; a.a0 = d->a0; a.drop = d->drop; a.xhat = d->xhat; a.invstd = d->invstd; a.a1 = d->a1; a.a2 = d->a2;
+    a.W1 = (const __nv_bfloat16*)d->W1; a.W2 = (const __nv_bfloat16*)d->W2; a.W3 = (const __nv_bfloat16*)d->W3;
+    a.bn_w = d->bn_w;
+    a.dW1 = d->dW1; a.db1 = d->db1; a.dbn_w = d->dbn_w; a.dbn_b = d->dbn_b; a.dW2 = d->dW2; a.db2 = d->db2;
+    a.dW3 = d->dW3; a.db3 = d->db3; a.dx = d->dx;
+    a.dz1 = scratch;                                   // device address, never the host-side symbol
+    a.training = d->training; a.accumulate = d->accumulate;
+    a.B = d->B; a.N0 = d->N0; a.N1 = d->N1; a.N2 = d->N2; a.N3 = d->N3;
+    DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&
+                    a.dW2 && a.db2 && a.dW3 && a.db3 && a.dx,
+                "dnb_head_backward_noalloc: null buffer");
     {
         const size_t smem = ((size_t)d->B * (d->N3 + 2 * d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
         if (d->B <= 16) head_bwd_l23_kernel<16><<<1, kB23Threads, smem, st>>>(a);

@@ -175,6 +175,14 @@ typedef struct DnbHeadBwdDesc {
 } DnbHeadBwdDesc;
 int dnb_head_backward(const DnbHeadBwdDesc* desc, void* stream);
 
+/* Allocation-free variant of dnb_head_backward (no counterpart in the reference: it exists for
+ * host programs that may not allocate device memory on this path).  Same inputs and outputs;
+ * desc->dz1 is ignored and the [B,N1] scratch is a 128 KiB __device__ array inside the library,
+ * held by every GPU that loads it.  Limits: B <= 64, N1 <= 512; anything larger is refused.  No
+ * cudaMalloc/cudaFree.  The first call on a device looks up the array's device address — make it
+ * before any stream capture on that device.  Calls share the array: overlapping calls on one GPU race. */
+int dnb_head_backward_noalloc(const DnbHeadBwdDesc* desc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
