@@ -35,6 +35,10 @@ struct Epi {
     const __nv_bfloat16* mask; long long ldmask;
     float* colsum;
     float alpha; int relu; int atomic_acc;
+    // BatchNorm-over-columns mode (rows = features, columns = the whole batch, N <= BN):
+    const float* bn_gamma; const float* bn_beta; float bn_eps;
+    float* bn_xhat; long long ldxh;      // [M, N] normalised values (saved for backward)
+    float* bn_invstd;                    // [M]
 };
 
 template <int BN>
@@ -137,6 +141,48 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         dnb::mbar_wait(tmem_full, 0);
         dnb::tc_fence_after();
         constexpr int CH = BN < 32 ? BN : 32;
+        // ---- optional BatchNorm over the columns of each row (batch statistics, biased variance):
+        // every thread owns one row with all N <= BN batch columns in TMEM, so mean/variance need no
+        // cross-thread reduction; TMEM is simply read three times (sum, centred squares, normalise).
+        const bool bn = epi.bn_gamma != nullptr;
+        float bn_mean = 0.f, bn_istd = 1.f, bn_g = 1.f, bn_b = 0.f;
+        const float row_bias = (epi.bias_m && m < M) ? epi.bias_m[m] : 0.f;
+        if (bn) {
+            float s1 = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / CH; ++c) {
+                uint32_t raw[CH];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * CH);
+                if constexpr (CH == 32) dnb::tmem_ld_32x32(taddr, raw);
+                else dnb::tmem_ld_32x16(taddr, raw);
+                dnb::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < CH; ++j)
+                    if (n0 + c * CH + j < N) s1 += __uint_as_float(raw[j]) * epi.alpha + row_bias;
+            }
+            bn_mean = s1 / (float)N;
+            float s2 = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / CH; ++c) {
+                uint32_t raw[CH];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * CH);
+                if constexpr (CH == 32) dnb::tmem_ld_32x32(taddr, raw);
+                else dnb::tmem_ld_32x16(taddr, raw);
+                dnb::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < CH; ++j)
+                    if (n0 + c * CH + j < N) {
+                        const float dlt = __uint_as_float(raw[j]) * epi.alpha + row_bias - bn_mean;
+                        s2 += dlt * dlt;
+                    }
+            }
+            bn_istd = rsqrtf(s2 / (float)N + epi.bn_eps);
+            if (m < M) {
+                bn_g = epi.bn_gamma[m];
+                bn_b = epi.bn_beta ? epi.bn_beta[m] : 0.f;
+                if (epi.bn_invstd) epi.bn_invstd[m] = bn_istd;
+            }
+        }
 #pragma unroll 1
         for (int c = 0; c < BN / CH; ++c) {
             uint32_t raw[CH];
@@ -147,12 +193,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int nb = n0 + c * CH;
             if (nb >= N) continue;   // warp-uniform
             float v[CH];
-            const float bm = (epi.bias_m && m < M) ? epi.bias_m[m] : 0.f;
+            const float bm = row_bias;
 #pragma unroll
             for (int j = 0; j < CH; ++j) {
                 float x = __uint_as_float(raw[j]) * epi.alpha + bm;
                 const int n = nb + j;
                 if (epi.bias_n && n < N) x += epi.bias_n[n];
+                if (bn) {
+                    const float xh = (x - bn_mean) * bn_istd;
+                    if (epi.bn_xhat && m < M && n < N) epi.bn_xhat[(long long)m * epi.ldxh + n] = xh;
+                    x = xh * bn_g + bn_b;
+                }
                 if (epi.relu) x = fmaxf(x, 0.f);
                 v[j] = x;
             }
@@ -290,11 +341,6 @@ DNB_EXPORT int dnb_gemm_bf16(const DnbGemmDesc* g, void* stream_) {
                         !g->colsum,
                     "split-K needs a plain fp32 output (it accumulates with atomics)");
     }
-    CUtensorMap ta, tb;
-    int rc = dnb_make_tmap_bf16_2d(&ta, g->A, g->M, g->K, g->lda, BM, BK);
-    if (rc) return rc;
-    rc = dnb_make_tmap_bf16_2d(&tb, g->B, g->N, g->K, g->ldb, bn, BK);
-    if (rc) return rc;
     Epi e;
     e.out = g->out; e.ldo = g->ldo; e.out_bf16 = g->out_bf16;
     e.outT = reinterpret_cast<__nv_bfloat16*>(g->outT); e.ldt = g->ldt;
@@ -303,6 +349,20 @@ DNB_EXPORT int dnb_gemm_bf16(const DnbGemmDesc* g, void* stream_) {
     e.colsum = g->colsum;
     e.alpha = g->alpha; e.relu = g->relu;
     e.atomic_acc = (splits > 1 || g->accumulate) ? 1 : 0;
+    e.bn_gamma = g->bn_gamma; e.bn_beta = g->bn_beta; e.bn_eps = g->bn_eps;
+    e.bn_xhat = g->bn_xhat; e.ldxh = g->ldxh; e.bn_invstd = g->bn_invstd;
+    if (g->bn_gamma) {
+        DNB_REQUIRE(splits == 1 && !g->accumulate && !g->bias_n, "BatchNorm epilogue: no split-K / accumulate / column bias");
+        if (bn < g->N) {      // the whole batch must sit in one tile
+            bn = g->N <= 16 ? 16 : g->N <= 32 ? 32 : g->N <= 64 ? 64 : g->N <= 128 ? 128 : 256;
+        }
+        DNB_REQUIRE(g->N <= 256, "BatchNorm epilogue needs the whole batch in one tile (N <= 256, got %d)", g->N);
+    }
+    CUtensorMap ta, tb;
+    int rc = dnb_make_tmap_bf16_2d(&ta, g->A, g->M, g->K, g->lda, BM, BK);
+    if (rc) return rc;
+    rc = dnb_make_tmap_bf16_2d(&tb, g->B, g->N, g->K, g->ldb, bn, BK);
+    if (rc) return rc;
     switch (bn) {
         case 16: return launch<16>(ta, tb, e, g->M, g->N, g->K, splits, st);
         case 32: return launch<32>(ta, tb, e, g->M, g->N, g->K, splits, st);

@@ -19,7 +19,7 @@ def _check_bf16_2d(t, name):
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, *, out_dtype=torch.float32,
               out_t: torch.Tensor | None = None, bias_n=None, bias_m=None, relu=False, mask=None, colsum=None,
-              alpha=1.0, accumulate=False, split_k=1, block_n=0, want_out=True):
+              alpha=1.0, accumulate=False, split_k=1, block_n=0, want_out=True, bn=None):
     """``out[M,N] = alpha * a[M,K] @ b[N,K].T`` with the fused epilogue of ``DnbGemmDesc``.
 
     ``a``/``b`` bf16 row-major (possibly strided views with ld % 8 == 0).  Returns ``out``
@@ -54,6 +54,13 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None,
         if mask.dtype != torch.bfloat16 or mask.shape != (M, N) or mask.stride(1) != 1:
             raise ValueError("mask must be [M,N] bf16")
         d.mask, d.ldmask = mask.data_ptr(), mask.stride(0)
+    if bn is not None:
+        # bn = dict(gamma [M], beta [M], eps, xhat [M,N] fp32 or None, invstd [M] or None)
+        d.bn_gamma, d.bn_beta, d.bn_eps = bn["gamma"].data_ptr(), bn["beta"].data_ptr(), float(bn.get("eps", 1e-5))
+        if bn.get("xhat") is not None:
+            d.bn_xhat, d.ldxh = bn["xhat"].data_ptr(), bn["xhat"].stride(0)
+        if bn.get("invstd") is not None:
+            d.bn_invstd = bn["invstd"].data_ptr()
     d.alpha, d.relu, d.accumulate, d.split_k, d.block_n = float(alpha), int(relu), int(accumulate), int(split_k), int(block_n)
     native.check(lib.dnb_gemm_bf16(ctypes.byref(d), native.stream()), "dnb_gemm_bf16")
     return out

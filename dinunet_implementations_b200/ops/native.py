@@ -156,6 +156,8 @@ class GemmDesc(ctypes.Structure):
         ("alpha", ctypes.c_float),
         ("relu", ctypes.c_int), ("accumulate", ctypes.c_int), ("split_k", ctypes.c_int), ("block_n", ctypes.c_int),
         ("split_k_auto", ctypes.c_int),
+        ("bn_gamma", ctypes.c_void_p), ("bn_beta", ctypes.c_void_p), ("bn_eps", ctypes.c_float),
+        ("bn_xhat", ctypes.c_void_p), ("ldxh", ctypes.c_longlong), ("bn_invstd", ctypes.c_void_p),
     ]
 
 

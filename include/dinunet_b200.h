@@ -96,6 +96,13 @@ typedef struct DnbGemmDesc {
                                            0: choose automatically when `accumulate` is set */
     int block_n;                        /* 0 = auto, else 16/32/64/128/256 */
     int split_k_auto;                   /* reserved (0) */
+    /* BatchNorm-over-columns epilogue (reference comps/fs/models.py:15,19: Linear -> BatchNorm1d with batch
+     * statistics -> ReLU): rows = features (weights are the A operand), columns = the whole batch (N <= 256).
+     * result = [relu](gamma * (x - mean_row) * invstd_row + beta).  Enabled when bn_gamma != NULL. */
+    const float* bn_gamma; const float* bn_beta;   /* [M] */
+    float bn_eps;
+    float* bn_xhat; long long ldxh;     /* optional [M,N] normalised values */
+    float* bn_invstd;                   /* optional [M] */
 } DnbGemmDesc;
 int dnb_gemm_bf16(const DnbGemmDesc* desc, void* stream);
 
@@ -182,6 +189,14 @@ int dnb_head_backward(const DnbHeadBwdDesc* desc, void* stream);
  * cudaMalloc/cudaFree.  The first call on a device looks up the array's device address — make it
  * before any stream capture on that device.  Calls share the array: overlapping calls on one GPU race. */
 int dnb_head_backward_noalloc(const DnbHeadBwdDesc* desc, void* stream);
+
+/* ---- K4: FreeSurfer MLP hidden layer backward through ReLU + BatchNorm(batch statistics)
+ * (reference comps/fs/models.py:13-23).  Activations are feature-major: daT / xhatT are [N, B]
+ * (leading dims ldd / ldx).  Writes dz as bf16 feature-major (dzT [N, ldzt]) and/or batch-major
+ * (dz [B, ldz]) for the weight- and data-gradient GEMMs, and the gamma/beta gradients. */
+int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, long long ldx, const float* gamma,
+                         const float* beta, const float* invstd, int N, int B, void* dzT, long long ldzt, void* dz,
+                         long long ldz, float* dgamma, float* dbeta, int accumulate, void* stream);
 
 #ifdef __cplusplus
 }
