@@ -31,10 +31,15 @@ def orthogonalize(P: torch.Tensor, eps: float = 1e-8) -> torch.Tensor:
     P = P.clone()
     n, r = P.shape
     scale = P.norm() + eps
+    # A linearly dependent column leaves a residual of ~machine-epsilon times its original size,
+    # not zero; normalising that noise would destroy orthogonality.  "Collapsed" is therefore judged
+    # relative to the column's norm before any projection (same rule as csrc/lowrank.cu).
+    rel = 1e-4 if P.dtype in (torch.float32, torch.bfloat16, torch.float16) else 1e-10
+    orig = P.norm(dim=0)
     for i in range(r):
         col = P[:, i]
         nrm = col.norm()
-        if nrm <= eps * scale:
+        if nrm <= max(eps * scale, rel * orig[i]):
             P[:, i] = 0
             continue
         col = col / nrm

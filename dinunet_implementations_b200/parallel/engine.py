@@ -61,7 +61,7 @@ class DeviceEngine:
             self.params += ordered_params(m)
         numel = flat_layout(self.params)[1]
         wire = wire_dtype_from_bits(self.cache.get("precision_bits", "32"))
-        need = numel * (4 + wire.itemsize + (2 if shadow_bf16 else 0)) + (1 << 20)
+        need = numel * (4 + wire.itemsize + (2 if shadow_bf16 else 0)) * 3 + (8 << 20)
         if group is None:
             import torch.distributed as dist
             ab = int(arena_bytes or need)
@@ -72,11 +72,47 @@ class DeviceEngine:
         self.group = group
         self.site = group.rank if site is None else site
         opt = str(self.cache.get("optimizer", "adam")).lower()
-        self.fused = FusedDSGD(group, numel, wire_dtype=wire, lr=float(self.cache.get("learning_rate", 1e-3)),
-                               optimizer=opt, momentum=float(self.cache.get("momentum", 0.0)), shadow_bf16=shadow_bf16,
-                               device_state=True)
+        lr_ = float(self.cache.get("learning_rate", 1e-3))
+        mom = float(self.cache.get("momentum", 0.0))
+        self.agg_engine = str(getattr(self.cache.get("agg_engine", "dSGD"), "value", self.cache.get("agg_engine", "dSGD")))
         holder = torch.nn.ModuleList(list(trainer.nn.values()))
-        self.fused.bind(holder, site=self.site, params=self.params)
+        if self.agg_engine == "dSGD":
+            self.fused = FusedDSGD(group, numel, wire_dtype=wire, lr=lr_, optimizer=opt, momentum=mom,
+                                   shadow_bf16=shadow_bf16, device_state=True)
+            self.fused.bind(holder, site=self.site, params=self.params)
+        elif self.agg_engine == "powerSGD":
+            from .lowrank_fused import DevicePowerSGD
+            self.fused = DevicePowerSGD(group, [self.params], rank=int(self.cache.get("powersgd_rank", 4)), lr=lr_,
+                                        optimizer=opt, momentum=mom, seed=int(self.cache.get("seed", 0)))
+            use_graph = False            # host-side control flow between the exchange phases
+        elif self.agg_engine == "rankDAD":
+            from ..distrib.rankdad import _LinearTap
+            from .lowrank_fused import DeviceRankDAD
+            taps, covered = [], set()
+            for m in trainer.nn.values():
+                if hasattr(m, "fused"):
+                    m.fused = False      # activations/deltas are captured on the eager nn.Linear calls
+                for mod in m.modules():
+                    if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad:
+                        taps.append(_LinearTap(mod))
+                        covered.add(id(mod.weight))
+                        if mod.bias is not None:
+                            covered.add(id(mod.bias))
+            dense = [p for p in self.params if id(p) not in covered]
+            self.fused = DeviceRankDAD(group, [self.params], [taps], [dense],
+                                       rank=int(self.cache.get("dad_reduction_rank", 10)),
+                                       num_pow_iters=int(self.cache.get("dad_num_pow_iters", 5)),
+                                       tol=float(self.cache.get("dad_tol", 1e-3)), lr=lr_, optimizer=opt, momentum=mom,
+                                       seed=int(self.cache.get("seed", 0)))
+            use_graph = False
+        else:
+            raise ValueError(f"unknown agg_engine {self.agg_engine!r}")
+        if self.agg_engine != "dSGD":
+            shadow = getattr(self.fused.opt[0].holder, "_bf16_shadow", None)
+            if shadow is not None:
+                for m in trainer.nn.values():
+                    for sub in m.modules():
+                        sub._bf16_shadow = shadow
         self.steps = 0
         # CUDA graph state
         self.use_graph = bool(use_graph)

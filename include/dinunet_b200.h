@@ -24,6 +24,8 @@ extern "C" {
 
 #define DNB_MAX_RANKS 8
 #define DNB_SIGNAL_BLOCKS 160
+#define DNB_ORTH_MAX_BATCH 32
+#define DNB_ORTH_MAX_COLS 64
 /* uint32 slots a signal pad needs: 2 phases x blocks x ranks */
 #define DNB_SIGNAL_WORDS (2 * DNB_SIGNAL_BLOCKS * DNB_MAX_RANKS)
 
@@ -197,6 +199,13 @@ int dnb_head_backward_noalloc(const DnbHeadBwdDesc* desc, void* stream);
 int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, long long ldx, const float* gamma,
                          const float* beta, const float* invstd, int N, int B, void* dzT, long long ldzt, void* dz,
                          long long ldz, float* dgamma, float* dbeta, int accumulate, void* stream);
+
+/* ---- K3b: in-place column orthonormalisation (modified Gram-Schmidt, fp32) of `count` tall-skinny
+ * matrices P[i] of shape [n[i], r[i]] with leading dimension ld[i]; one CTA per matrix, one launch per
+ * 32 matrices.  powerSGD's orthogonalise(P) and the rankDAD subspace iteration (engine names
+ * comps/__init__.py:15-16).  Pointer / shape arrays are HOST arrays. */
+int dnb_orthogonalize_batch(float* const* P, const int* n, const int* r, const int* ld, int count, float eps,
+                            void* stream);
 
 #ifdef __cplusplus
 }
