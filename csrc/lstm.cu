@@ -111,11 +111,25 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     // ---- one-time: weight slice -> swizzled smem, zero h_{-1}
     const __nv_bfloat16* W = a.Whh[dir];
     const int chunks_per_row = H / 8;
-    for (int idx = tid; idx < 128 * chunks_per_row; idx += kThreads) {
-        const int r = idx / chunks_per_row, ch = idx % chunks_per_row;
-        const int grow = (r >> 5) * H + cta * U + (r & 31);
-        const uint4 v = *reinterpret_cast<const uint4*>(W + (size_t)grow * H + ch * 8);
-        *reinterpret_cast<uint4*>(sA + sw128_off(128, r, ch * 8)) = v;
+    for (int base = 0; base < 128 * chunks_per_row; base += kThreads * 8) {
+        uint4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {                     // 8 independent 16-byte loads in flight per thread
+            const int idx = base + u * kThreads + tid;
+            if (idx < 128 * chunks_per_row) {
+                const int r = idx / chunks_per_row, ch = idx % chunks_per_row;
+                const int gr = (r >> 5) * H + cta * U + (r & 31);
+                v[u] = *reinterpret_cast<const uint4*>(W + (size_t)gr * H + ch * 8);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * kThreads + tid;
+            if (idx < 128 * chunks_per_row) {
+                const int r = idx / chunks_per_row, ch = idx % chunks_per_row;
+                *reinterpret_cast<uint4*>(sA + sw128_off(128, r, ch * 8)) = v[u];
+            }
+        }
     }
     if (H & 63) {   // zero the unused tail of the last k-block so stale smem never feeds the MMA
         for (int idx = tid; idx < 128 * (KB * 8 - chunks_per_row); idx += kThreads) {
@@ -166,9 +180,11 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     if (b2_ok) *reinterpret_cast<uint2*>(hp_ptr) = make_uint2(0, 0);      // h_{-1} = 0 in the saved sequence
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
-    const uint64_t da_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sA));
-    const uint64_t db_base0 = dnb::umma_desc_k_sw128(dnb::smem_u32(sH));
-    const uint64_t db_base1 = dnb::umma_desc_k_sw128(dnb::smem_u32(sH + h_bytes));
+    // broadcast from lane 0 so the compiler keeps descriptors / TMEM address in uniform registers
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t da_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sA), 0));
+    const uint64_t db_base0 = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sH), 0));
+    const uint64_t db_base1 = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sH + h_bytes), 0));
     const int ksteps = H / 16;
     // destination of this thread's 16-byte h chunk (even ug lanes send): same offset in every CTA
     const uint32_t chunk_off = sw128_off(NB, b2, cta * U + (ug & ~1) * 4);
@@ -196,14 +212,14 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             // Warp-uniform control flow + elect.sync: the descriptors stay in uniform registers and
             // each tcgen05.mma is a single UTCHMMA (a divergent `tid == 0` branch makes ptxas wrap
             // every MMA in a lane-election loop, ~60 cycles apiece).
-            if (t > 0) dnb::mbar_wait_cluster(&hbar[t & 1], ((t - 1) >> 1) & 1);   // h_{t-1} complete
+            if (t > 0) dnb::mbar_wait(&hbar[t & 1], ((t - 1) >> 1) & 1);   // h_{t-1} complete (complete_tx, as for TMA)
             dnb::tc_fence_after();
             const uint64_t db_base = (t & 1) ? db_base1 : db_base0;
             if (dnb::elect_one()) {
                 if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
 #pragma unroll
                 for (int k = 0; k < 16; ++k)
-                    if (k < ksteps) dnb::umma_bf16_ss(tmem_base, da_base + koff_a(k), db_base + koff_b(k), idesc, k != 0);
+                    if (k < ksteps) dnb::umma_bf16_ss(tmem_u, da_base + koff_a(k), db_base + koff_b(k), idesc, k != 0);
                 dnb::umma_commit(mma_bar);
             }
             __syncwarp();
@@ -233,12 +249,17 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
         dnb::tmem_ld_wait();
         DNB_STAMP(4);
+        // 16 independent activation chains per thread; the gate type is warp-uniform, so the branch
+        // sits outside the unrolled loop and the MUFU ops of different batch columns overlap
 #pragma unroll
-        for (int b = 0; b < NB; ++b) {
-            const float p = __uint_as_float(acc[b]) + px[b] + bias;
-            pst[b] = p;                                           // saved for BPTT (stored next step)
-            const float act = (warp < 3) ? dnb::sigmoid_fast(dnb::sigmoid_fast(p)) : dnb::tanh_fast(p);
-            sAct[(warp * NB + b) * U + lane] = act;
+        for (int b = 0; b < NB; ++b) pst[b] = __uint_as_float(acc[b]) + px[b] + bias;   // saved for BPTT
+        float* act_row = sAct + warp * NB * U + lane;
+        if (warp < 3) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::sigmoid_fast(dnb::sigmoid_fast(pst[b]));
+        } else {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::tanh_fast(pst[b]);
         }
         DNB_STAMP(5);
         dnb::tc_fence_before();
@@ -271,8 +292,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             if ((ug & 1) == 0) {
                 const uint4 chunk = make_uint4(hb.x, hb.y, other.x, other.y);
                 const uint32_t d_off = send_data[(t + 1) & 1], b_off = send_bar[(t + 1) & 1];
-                for (int peer = 0; peer < ncta; ++peer)
-                    dnb::st_async_v4(dnb::mapa(d_off, peer), chunk, dnb::mapa(b_off, peer));
+#pragma unroll
+                for (int peer = 0; peer < kMaxCtas; ++peer)
+                    if (peer < ncta) dnb::st_async_v4(dnb::mapa(d_off, peer), chunk, dnb::mapa(b_off, peer));
             }
         }
         DNB_STAMP(7);
@@ -343,12 +365,29 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     sDb[tid] = 0.f;
     __syncthreads();
     const __nv_bfloat16* W = a.Whh[dir];
-    for (int idx = tid; idx < 128 * H; idx += kThreads) {
-        const int jl = idx / H, kp = idx % H;            // jl: local gate row (q*32+u), kp: hidden unit
+    // thread = local gate row jl (consecutive lanes -> consecutive smem columns, no bank conflicts);
+    // each trip loads 4 x 8 hidden units of that row with independent 16-byte loads
+    {
+        const int jl = tid;                               // kThreads == 128 == number of local gate rows
         const int grow = (jl >> 5) * H + cta * U + (jl & 31);
-        const __nv_bfloat16 v = W[(size_t)grow * H + kp];
-        const int mt = kp >> 7, r = kp & 127;
-        *reinterpret_cast<__nv_bfloat16*>(sA + mt * tile_bytes + sw128_off(128, r, jl)) = v;
+        const __nv_bfloat16* wrow = W + (size_t)grow * H;
+        for (int c0 = 0; c0 < H / 8; c0 += 4) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c0 + u < H / 8) v[u] = *reinterpret_cast<const uint4*>(wrow + (c0 + u) * 8);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c0 + u < H / 8) {
+                    const uint32_t w32[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int kp = (c0 + u) * 8 + e;
+                        const uint16_t bits = (uint16_t)((e & 1) ? (w32[e >> 1] >> 16) : (w32[e >> 1] & 0xFFFFu));
+                        *reinterpret_cast<uint16_t*>(sA + (kp >> 7) * tile_bytes + sw128_off(128, kp & 127, jl)) = bits;
+                    }
+                }
+        }
     }
     if (warp == 0) {
         if (lane == 0) {
@@ -386,8 +425,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         for (int j = 0; j < 4; ++j) dbacc[q][j] = 0.f;
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
-    const uint64_t da_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sA));
-    const uint64_t db_base = dnb::umma_desc_k_sw128(dnb::smem_u32(sB));
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t da_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sA), 0));
+    const uint64_t db_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sB), 0));
     const uint64_t tile_off = (uint64_t)(tile_bytes / 16);
     // where this warp's partial-dh blocks go: tile mt of warp w belongs to CTA mt*4 + w
     const uint32_t red_local[2] = {dnb::smem_u32(sRed + ((size_t)cta * U + lane) * NB),
@@ -434,7 +474,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
                     if (mt < MT) {
 #pragma unroll
                         for (int k = 0; k < 8; ++k)
-                            dnb::umma_bf16_ss(tmem_base + mt * NB, da_base + mt * tile_off + koff_a(k),
+                            dnb::umma_bf16_ss(tmem_u + mt * NB, da_base + mt * tile_off + koff_a(k),
                                               db_base + koff_b(k), idesc, k != 0);
                     }
                 dnb::umma_commit(mma_bar);
@@ -498,15 +538,18 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
                 }
             DNB_STAMP(4);
             dnb::tc_fence_before();
-            dnb::mbar_wait_cluster(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
+            dnb::mbar_wait(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
             DNB_STAMP(5);
             const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB + b2;
+            float part[kMaxCtas][4];
 #pragma unroll
-            for (int src = 0; src < kMaxCtas; ++src)       // constant offsets, independent loads
-                if (src < ncta) {
+            for (int src = 0; src < kMaxCtas; ++src)       // constant offsets; all loads issued before the adds
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) dh[j] += red_par[(src * U + j) * NB];
-                }
+                for (int j = 0; j < 4; ++j) part[src][j] = (src < ncta) ? red_par[(src * U + j) * NB] : 0.f;
+#pragma unroll
+            for (int src = 0; src < kMaxCtas; ++src)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dh[j] += part[src][j];
         }
         DNB_STAMP(6);
         float dp[4][4];
