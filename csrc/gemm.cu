@@ -313,6 +313,7 @@ DNB_EXPORT int dnb_gemm_bf16(const DnbGemmDesc* g, void* stream_) {
         double best = 1e30;
         for (int cand : {256, 128, 64, 32}) {
             if (cand > 32 && g->N <= cand / 2) continue;          // mostly padding
+            if (cand == 256 && total_kt < 16) continue;            // short K: the 256-column epilogue dominates
             const long tiles = (long)mt * ((g->N + cand - 1) / cand);
             const long waves = (tiles + sms - 1) / sms;
             const double cost = (double)waves * (6.0 + (double)total_kt * (0.35 + cand / 128.0 * 0.5) + cand / 64.0);

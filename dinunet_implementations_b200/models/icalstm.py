@@ -98,6 +98,10 @@ class ICALstm(nn.Module):
         order += [c.i2h.bias for c in cells] + [c.h2h.bias for c in cells]
         return order
 
+    def dad_capture_keys(self):
+        """Linear modules whose (delta, activation) pairs the fused backward can hand to rankDAD."""
+        return [n for n, m in self.named_modules() if isinstance(m, nn.Linear)]
+
     def forward_eager(self, x):
         B, S = x.shape[0], x.shape[1]
         e = self.encoder(x.reshape(B * S, -1)).view(B, S, -1)

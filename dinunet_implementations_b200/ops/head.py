@@ -58,4 +58,5 @@ def head_backward(dlogits, saved, grads, accumulate=True):
     d.training, d.accumulate = int(saved["training"]), int(accumulate)
     d.B, d.N0, d.N1, d.N2, d.N3 = B, N0, N1, N2, N3
     native.check(lib.dnb_head_backward(ctypes.byref(d), native.stream()), "dnb_head_backward")
+    saved["dz1"] = dz1          # gradient at the BatchNorm input (rankDAD capture reads it)
     return dx

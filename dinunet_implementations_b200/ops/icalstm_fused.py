@@ -130,16 +130,44 @@ class _ICALstmFn(torch.autograd.Function):
         bn = cls[2]
         dev = dlogits.device
 
+        capture = getattr(model, "_dad_capture", False)
         # 6. head backward (accumulates into the parameter gradients)
         grads = dict(dW1=_grad_buf(cls[1].weight), db1=_grad_buf(cls[1].bias), dbn_w=_grad_buf(bn.weight),
                      dbn_b=_grad_buf(bn.bias), dW2=_grad_buf(cls[4].weight), db2=_grad_buf(cls[4].bias),
                      dW3=_grad_buf(cls[6].weight), db3=_grad_buf(cls[6].bias))
         dHmean = head_backward(dlogits, head_saved, grads, accumulate=True)
+        if capture:
+            # rankDAD: ship factors of (delta, activation) instead of the weight gradients.  The head is
+            # tiny (batch rows only), so its pairs are rebuilt from the saved activations with torch ops.
+            hs = head_saved
+            B_ = dlogits.shape[0]
+            dl = dlogits.float()
+            dz2 = (dl @ hs["W3"].float()) * (hs["a2"] > 0)
+            pairs = {"classifier.6": (dl, hs["a2"]), "classifier.4": (dz2, hs["a1"])}
+            # dz1 is what head_backward handed from its first to its second launch
+            pairs["classifier.1"] = (hs["dz1"], hs["a0"])
+            model._dad_pairs = pairs
 
         # 7. BPTT
         db_ih = [_grad_buf(c.i2h.bias) for c in cells]
         db_hh = [_grad_buf(c.h2h.bias) for c in cells]
         dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True)
+
+        if capture:
+            # LSTM pairs: delta = dP (per direction), activations = encoder output / previous hidden state
+            for dd in range(D):
+                sl = slice(dd * 4 * H, (dd + 1) * 4 * H)
+                model._dad_pairs[f"lstm.lstms.{dd}.i2h"] = (dP[:, sl], enc)
+                model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (dP[:, sl], Hprev[:, dd * H:(dd + 1) * H])
+            if D == 2 and _adjacent(w_ih[0], w_ih[1]):
+                w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
+            else:
+                w_cat = torch.cat(w_ih, 0)
+            w_ihT = transpose_bf16(w_cat)
+            d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
+            gemm_bf16(dP, w_ihT, out=d_enc, mask=enc)
+            model._dad_pairs["encoder.0"] = (d_enc, xT.t())
+            return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
         # 8. K-major operands for the weight-gradient GEMMs
         dPT = transpose_bf16(dP)                    # [D*4H, S*B]

@@ -88,13 +88,17 @@ class DeviceEngine:
         elif self.agg_engine == "rankDAD":
             from ..distrib.rankdad import _LinearTap
             from .lowrank_fused import DeviceRankDAD
+            from .lowrank_fused import CapturedTap
             taps, covered = [], set()
             for m in trainer.nn.values():
-                if hasattr(m, "fused"):
-                    m.fused = False      # activations/deltas are captured on the eager nn.Linear calls
-                for mod in m.modules():
+                fused_capture = bool(getattr(m, "fused", False)) and hasattr(m, "dad_capture_keys")
+                if fused_capture:
+                    m._dad_capture = True    # the fused backward hands over (delta, activation) pairs
+                elif hasattr(m, "fused"):
+                    m.fused = False          # otherwise capture on the eager nn.Linear calls
+                for name, mod in m.named_modules():
                     if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad:
-                        taps.append(_LinearTap(mod))
+                        taps.append(CapturedTap(mod, m, name) if fused_capture else _LinearTap(mod))
                         covered.add(id(mod.weight))
                         if mod.bias is not None:
                             covered.add(id(mod.bias))

@@ -88,7 +88,7 @@ class _LocalOptim:
     def __init__(self, device, params, lr, optimizer="adam", momentum=0.0):
         self.params = params
         offs, total = flat_layout(params)
-        self.group = SiteGroup.local(1, total * 8 + (1 << 20), device)
+        self.group = SiteGroup.local(1, total * 12 + (4 << 20), device)
         self.f = FusedDSGD(self.group, total, lr=lr, optimizer=optimizer, momentum=momentum, mode="one_shot",
                            name="local", device_state=True, shadow_bf16=True)
         self.holder = torch.nn.ParameterList(params)
@@ -187,6 +187,25 @@ class DevicePowerSGD:
             for j, i in enumerate(self.vec_ix):
                 ps[i].grad.copy_(Pm[li][self.v_off[j]:self.v_off[j] + ps[i].numel()].view_as(ps[i]))
             self.opt[li].step()
+
+
+class CapturedTap:
+    """Stands in for ``distrib.rankdad._LinearTap`` when the fused kernels hand over the
+    (delta, activation) pair of a Linear directly (``model._dad_pairs[key]``), so no module hooks
+    and no eager forward are needed."""
+
+    def __init__(self, module: torch.nn.Linear, model: torch.nn.Module, key: str):
+        self.module, self.model, self.key = module, model, key
+
+    def pop(self):
+        pairs = getattr(self.model, "_dad_pairs", None) or {}
+        if self.key not in pairs:
+            return None, None
+        D, A = pairs.pop(self.key)
+        D, A = D.float(), A.float()
+        if self.module.bias is not None:
+            A = torch.cat([A, torch.ones(A.shape[0], 1, device=A.device)], 1)
+        return D, A
 
 
 class DeviceRankDAD:

@@ -112,3 +112,33 @@ def test_device_engine_with_lowrank_aggregation_trains(engine):
     batch = {"inputs": torch.randn(8, 8, 8, 5, generator=g), "labels": torch.randint(0, 2, (8,), generator=g)}
     losses = [float(eng.train_step(batch)["loss"].detach()) for _ in range(12)]
     assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+
+
+def test_fused_capture_pairs_reproduce_the_weight_gradients():
+    """The (delta, activation) pairs handed over by the fused ICA-LSTM backward reconstruct the same
+    gradients the fused weight-gradient GEMMs produce (delta^T . activation, bias = column sums)."""
+    import copy
+    from dinunet_implementations_b200.models import ICALstm
+    torch.manual_seed(0)
+    kw = dict(input_size=64, hidden_size=128, num_comps=12, window_size=6, num_cls=2)
+    a = ICALstm(fused=True, **kw).cuda()
+    b = ICALstm(fused=True, **kw).cuda()
+    b.load_state_dict(copy.deepcopy(a.state_dict()))
+    for m in (a, b):
+        m.train(); m.classifier[0].p = 0.0
+    b._dad_capture = True
+    x = torch.randn(8, 9, 12, 6, device="cuda")
+    y = torch.randint(0, 2, (8,), device="cuda")
+    torch.nn.functional.cross_entropy(a(x)[0], y).backward()
+    torch.nn.functional.cross_entropy(b(x)[0], y).backward()
+    torch.cuda.synchronize()
+    mods_a = dict(a.named_modules())
+    assert set(b._dad_pairs) == set(b.dad_capture_keys())
+    for key, (D, A) in b._dad_pairs.items():
+        G = D.float().t() @ A.float()
+        ref = mods_a[key].weight.grad
+        s = max(ref.abs().max().item(), 1e-6)
+        assert torch.allclose(G, ref, atol=0.05 * s), (key, (G - ref).abs().max().item(), s)
+        bref = mods_a[key].bias.grad
+        sb = max(bref.abs().max().item(), 1e-6)
+        assert torch.allclose(D.float().sum(0), bref, atol=0.05 * sb), (key, "bias")
