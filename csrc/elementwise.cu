@@ -103,7 +103,50 @@ __global__ void softmax_ce_kernel(const float* __restrict__ logits, const long l
     if (lane == 0 && loss) atomicAdd(loss, (lse - z[y]) * invB);
 }
 
+// K9: device-side metric accumulators.  One tiny launch per step appends the batch's positive-class
+// scores and labels to a device buffer (ROC-AUC needs every pair), bumps the confusion counts at the
+// given threshold and the running loss sum — no host sync in the training loop (the reference pays a
+// loss.item() per iteration, comps/fs/__init__.py:61).  state = {cursor, tp, fp, tn, fn}; lossacc = {sum, n}.
+__global__ void metrics_append_kernel(const float* __restrict__ scores_in, long long ld, int col,
+                                      const long long* __restrict__ labels, const float* __restrict__ loss, int B,
+                                      float* __restrict__ scores, int* __restrict__ labs, int cap,
+                                      unsigned long long* __restrict__ state, float* __restrict__ lossacc, float thr) {
+    const unsigned long long cur = state[0];
+    __syncthreads();
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        const float s = scores_in[(long long)b * ld + col];
+        const int y = (int)labels[b];
+        const unsigned long long pos = cur + b;
+        if (pos < (unsigned long long)cap) {
+            scores[pos] = s;
+            labs[pos] = y;
+        }
+        const int p = s >= thr;
+        atomicAdd(&state[1 + (p ? (y ? 0 : 1) : (y ? 3 : 2))], 1ull);      // tp, fp, tn, fn
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        state[0] = cur + B;
+        if (loss) {
+            lossacc[0] += loss[0] * (float)B;
+            lossacc[1] += (float)B;
+        }
+    }
+}
+
 }  // namespace
+
+DNB_EXPORT int dnb_metrics_append(const float* scores_in, long long ld, int col, const long long* labels,
+                                  const float* loss, int B, float* scores, int* labs, int cap,
+                                  unsigned long long* state, float* lossacc, float thr, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(scores_in && labels && scores && labs && state && lossacc && B > 0 && cap > 0,
+                "dnb_metrics_append: bad arguments");
+    metrics_append_kernel<<<1, 128, 0, st>>>(scores_in, ld, col, labels, loss, B, scores, labs, cap, state, lossacc, thr);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
 
 DNB_EXPORT int dnb_cast_time_major(const float* x, void* rows, long long ldr, void* colsT, long long ldt, int B, int S,
                                    int F, void* stream_) {

@@ -50,6 +50,19 @@ def orthogonalize(P: torch.Tensor, eps: float = 1e-8) -> torch.Tensor:
     return P
 
 
+def _orth_fast(P: torch.Tensor) -> torch.Tensor:
+    """``orthogonalize`` for the hot path: one launch of the batched sm_100a kernel
+    (``dnb_orthogonalize_batch``) when ``P`` is an fp32 CUDA matrix, the Python loop otherwise."""
+    if P.is_cuda and P.dtype == torch.float32 and P.shape[1] <= 64:
+        from ..ops import native
+        if native.available():
+            from ..parallel.lowrank_fused import orthogonalize_batch
+            Q = P.contiguous().clone()
+            orthogonalize_batch([Q])
+            return Q
+    return orthogonalize(P)
+
+
 def _seeded_normal(shape, seed, device, dtype):
     g = torch.Generator(device="cpu")
     g.manual_seed(int(seed) % (2 ** 31 - 1))
@@ -83,14 +96,18 @@ def dad_compress(delta: torch.Tensor, act: torch.Tensor, rank: int, num_pow_iter
     prev = None
     used = 0
     U = None
+    # On a CUDA device the early exit would cost a host sync per iteration (reading ‖V‖), so the
+    # device path always runs ``num_pow_iters`` rounds — a superset of the work, never less accurate.
+    check_tol = not delta.is_cuda
     for it in range(max(int(num_pow_iters), 1)):
-        U = orthogonalize(delta.t() @ (act @ V))        # [out, r]
+        U = _orth_fast(delta.t() @ (act @ V))           # [out, r]
         V = act.t() @ (delta @ U)                        # [in, r]  (= Gᵀ U, carries σ)
         used = it + 1
-        energy = float(V.norm())
-        if prev is not None and abs(energy - prev) <= tol * max(energy, 1e-30):
-            break
-        prev = energy
+        if check_tol:
+            energy = float(V.norm())
+            if prev is not None and abs(energy - prev) <= tol * max(energy, 1e-30):
+                break
+            prev = energy
     return U.t().contiguous(), V.t().contiguous(), used
 
 

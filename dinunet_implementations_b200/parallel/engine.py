@@ -50,7 +50,8 @@ class DeviceEngine:
     otherwise the engine silently keeps stepping eagerly."""
 
     def __init__(self, trainer, group: SiteGroup | None = None, arena_bytes: int | None = None, site: int | None = None,
-                 shadow_bf16: bool = True, use_graph: bool = False, graph_warmup: int = 3):
+                 shadow_bf16: bool = True, use_graph: bool = False, graph_warmup: int = 3,
+                 track_metrics: bool = False, metric_capacity: int = 1 << 20):
         self.trainer = trainer
         self.cache = trainer.cache
         self.device = trainer.device["gpu"]
@@ -118,6 +119,10 @@ class DeviceEngine:
                     for sub in m.modules():
                         sub._bf16_shadow = shadow
         self.steps = 0
+        self.train_metrics = None
+        if track_metrics:
+            from ..ops.metrics import DeviceMetricBuffer
+            self.train_metrics = DeviceMetricBuffer(self.device, capacity=int(metric_capacity))
         # CUDA graph state
         self.use_graph = bool(use_graph)
         self.graph_warmup = int(graph_warmup)
@@ -142,7 +147,18 @@ class DeviceEngine:
         it = self.trainer.iteration(batch)
         it["loss"].backward()
         self.fused.step()
+        if self.train_metrics is not None and it.get("out") is not None and "labels" in batch:
+            # K9: scores / labels / loss of this step go to device accumulators (inside the graph too)
+            self.train_metrics.append(it["out"], batch["labels"], it["loss"])
         return it
+
+    def epoch_metrics(self, reset=True):
+        """``(averages, metrics)`` of the training steps since the last call — one host sync."""
+        if self.train_metrics is None:
+            return self.trainer.new_averages(), self.trainer.new_metrics()
+        avg, auc, prf = self.train_metrics.collect(reset)
+        want_auc = str(self.cache.get("monitor_metric", "auc")).lower() == "auc"
+        return avg, (auc if want_auc else prf)
 
     def _capture(self, dev_batch):
         self._static_in = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in dev_batch.items()}

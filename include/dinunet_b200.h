@@ -207,6 +207,14 @@ int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, lo
 int dnb_orthogonalize_batch(float* const* P, const int* n, const int* r, const int* ld, int count, float eps,
                             void* stream);
 
+/* K9: device-side metric accumulators (reference hooks: new_metrics().add / new_averages().add,
+ * comps/fs/__init__.py:58-61, comps/icalstm/__init__.py:64-68).  Appends column `col` of scores_in [B, ld]
+ * and the labels to scores/labs (capacity cap), updates state = {cursor, tp, fp, tn, fn} (uint64) at
+ * threshold thr and lossacc = {sum(loss*B), sum(B)}.  loss may be NULL. */
+int dnb_metrics_append(const float* scores_in, long long ld, int col, const long long* labels, const float* loss,
+                       int B, float* scores, int* labs, int cap, unsigned long long* state, float* lossacc, float thr,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif
