@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <mutex>
@@ -177,4 +178,35 @@ DNB_EXPORT int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n,
     }
     for (auto& t : th) t.join();
     return 0;
+}
+
+// ------------------------------------------------------------------------------------ native data loading
+// One FreeSurfer aseg-stats file: a header line, then `name<TAB>value` rows (66 of them in the
+// reference's test_fsl data).  Returns the number of values parsed (negative on error); with
+// `normalise` every value is divided by the subject's own maximum, as the reference dataset does
+// (comps/fs/__init__.py:37).  Replaces a pandas.read_csv per sample per epoch.
+DNB_EXPORT int dnb_parse_aseg(const char* path, double* out, int max_n, int normalise) {
+    if (!path || !out || max_n <= 0) return -1;
+    FILE* f = fopen(path, "r");
+    if (!f) return -2;
+    char line[4096];
+    int n = 0;
+    bool first = true;
+    double mx = 0.0;
+    while (fgets(line, sizeof(line), f)) {
+        if (first) { first = false; continue; }
+        char* tab = strchr(line, '\t');
+        if (!tab) continue;
+        char* end = nullptr;
+        const double v = strtod(tab + 1, &end);
+        if (end == tab + 1) continue;
+        if (n < max_n) out[n] = v;
+        if (n == 0 || v > mx) mx = v;
+        ++n;
+    }
+    fclose(f);
+    if (n > max_n) return -3;
+    if (normalise && n > 0 && mx != 0.0)
+        for (int i = 0; i < n; ++i) out[i] /= mx;
+    return n;
 }

@@ -38,7 +38,16 @@ def read_covariates(path, index_column=None):
 
 
 def parse_aseg_stats(path, normalise=True):
-    """One subject's volumes as float64 → divided by the subject's max (reference ``:37``)."""
+    """One subject's volumes as float64 → divided by the subject's max (reference ``:37``).
+    Uses the native parser of libdinunet_b200 when it is built, else pure Python."""
+    from ..ops import native
+    if native.available(cpu_only=True) and hasattr(native.lib(), "dnb_parse_aseg"):
+        import ctypes
+        buf = np.empty(4096, dtype=np.float64)
+        n = native.lib().dnb_parse_aseg(os.fsencode(path), ctypes.c_void_p(buf.ctypes.data), ctypes.c_int(buf.size),
+                                        ctypes.c_int(int(normalise)))
+        if n >= 0:
+            return buf[:n].copy()
     vals = []
     with open(path) as f:
         next(f, None)                     # "Measure:volume<TAB>subjectN"

@@ -48,6 +48,10 @@ int dnb_enable_peer_access(int peer_device);
  * Replaces the aggregator's multiprocessing pool (reference remote.py:20-21). */
 int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n, int is_half, float* out, int n_threads);
 
+/* Native parser for one FreeSurfer aseg-stats file (reference comps/fs/__init__.py:33-39): returns the
+ * number of values written to out (<0 on error); normalise != 0 divides by the subject's maximum. */
+int dnb_parse_aseg(const char* path, double* out, int max_n, int normalise);
+
 /* ---- K1: dSGD all-reduce fused with Adam/SGD (reference engine "dSGD", comps/__init__.py:14;
  *      precision_bits compspec.json:161-176) ----------------------------------------------- */
 typedef struct DnbDsgdDesc {
