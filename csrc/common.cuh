@@ -256,6 +256,15 @@ __device__ __forceinline__ void st_async_v4(uint32_t remote_addr, uint4 v, uint3
                  ::"r"(remote_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(remote_bar)
                  : "memory");
 }
+// Bulk copy of a contiguous block from this CTA's shared memory into (possibly another CTA's)
+// shared memory; the destination CTA's mbarrier receives ONE complete_tx(bytes) when it has landed.
+// bytes must be a multiple of 16, both addresses 16-byte aligned.
+__device__ __forceinline__ void bulk_copy_smem_to_cluster(uint32_t dst_cluster_addr, uint32_t src_cta_addr,
+                                                          uint32_t bytes, uint32_t bar_cluster_addr) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_cluster_addr), "r"(src_cta_addr), "r"(bytes), "r"(bar_cluster_addr)
+                 : "memory");
+}
 __device__ __forceinline__ void st_cluster_u32(uint32_t addr, uint32_t v) {
     asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }

@@ -343,7 +343,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     float* sRed = reinterpret_cast<float*>(sB + 2 * NB * 128);   // [2][ncta][U][NB]
     const int ncta = dnb::cluster_nctarank();
     float* sDb = sRed + 2 * ncta * U * NB;               // [128] bias-gradient reduction
-    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sDb + 128);
+    float* sStg = sDb + 128;                             // [2 parity][4 warps][2 tiles][U*NB] outgoing partial blocks
+    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStg + 2 * 4 * 2 * U * NB);
     uint64_t* rbar = mma_bar + 1;                        // [2]: "all partial dh blocks of round n arrived"
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rbar + 2);
 
@@ -430,8 +431,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const uint64_t db_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sB), 0));
     const uint64_t tile_off = (uint64_t)(tile_bytes / 16);
     // where this warp's partial-dh blocks go: tile mt of warp w belongs to CTA mt*4 + w
-    const uint32_t red_local[2] = {dnb::smem_u32(sRed + ((size_t)cta * U + lane) * NB),
-                                   dnb::smem_u32(sRed + (size_t)ncta * U * NB + ((size_t)cta * U + lane) * NB)};
+    const uint32_t red_blk[2] = {dnb::smem_u32(sRed + (size_t)cta * U * NB),
+                                 dnb::smem_u32(sRed + (size_t)ncta * U * NB + (size_t)cta * U * NB)};
     const uint32_t rbar_local[2] = {dnb::smem_u32(&rbar[0]), dnb::smem_u32(&rbar[1])};
     const uint32_t sB_off[4] = {sw128_off(NB, b2, 0 * U + ug * 4), sw128_off(NB, b2, 1 * U + ug * 4),
                                 sw128_off(NB, b2, 2 * U + ug * 4), sw128_off(NB, b2, 3 * U + ug * 4)};
@@ -521,6 +522,10 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             dnb::mbar_wait(mma_bar, n & 1);
             dnb::tc_fence_after();
             DNB_STAMP(3);
+            // Each warp owns a 32-unit x 16-batch block of the partial dh per tile.  It is staged in
+            // shared memory (16-byte chunks XOR-swizzled by unit so the owner's column reads spread over
+            // banks) and shipped to the owning CTA with ONE bulk copy = one complete_tx on its barrier
+            // (per-thread st.async cost one mbarrier update per 16 bytes, 768 per CTA and step).
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
                 if (mt < MT) {
@@ -529,18 +534,25 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
                     dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v);
                     dnb::tmem_ld_wait();
                     if (dest < ncta) {
-                        const uint32_t remote = dnb::mapa(red_local[n & 1], dest);
-                        const uint32_t rb = dnb::mapa(rbar_local[n & 1], dest);
+                        float* stg = sStg + ((((n & 1) * 4 + warp) * 2 + mt) * U * NB);
+                        const int swz = (lane >> 2) & 3;
 #pragma unroll
-                        for (int x = 0; x < NB; x += 4)
-                            dnb::st_async_v4(remote + x * 4, make_uint4(v[x], v[x + 1], v[x + 2], v[x + 3]), rb);
+                        for (int x = 0; x < 4; ++x)
+                            *reinterpret_cast<uint4*>(stg + lane * NB + ((x ^ swz) << 2)) =
+                                make_uint4(v[4 * x], v[4 * x + 1], v[4 * x + 2], v[4 * x + 3]);
+                        dnb::fence_proxy_async_smem();
+                        __syncwarp();
+                        if (dnb::elect_one())
+                            dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk[n & 1], dest), dnb::smem_u32(stg),
+                                                           U * NB * 4, dnb::mapa(rbar_local[n & 1], dest));
                     }
                 }
             DNB_STAMP(4);
             dnb::tc_fence_before();
             dnb::mbar_wait(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
             DNB_STAMP(5);
-            const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB + b2;
+            const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB +
+                                   ((((b2 >> 2) ^ (ug & 3)) << 2) | (b2 & 3));
             float part[kMaxCtas][4];
 #pragma unroll
             for (int src = 0; src < kMaxCtas; ++src)       // constant offsets; all loads issued before the adds
@@ -694,6 +706,6 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
             if (a.db_b[i]) DNB_CUDA_CHECK(cudaMemsetAsync(a.db_b[i], 0, sizeof(float) * 4 * d->H, st));
         }
     }
-    const size_t smem = (size_t)MT * 2 * 128 * 128 + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + 128 + 1024;
+    const size_t smem = (size_t)MT * 2 * 128 * 128 + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + (size_t)2 * 4 * 2 * U * NB * 4 + 128 + 1024;
     return launch_cluster(lstm_bwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }

@@ -52,6 +52,16 @@ def _grad_buf(p):
     return p.grad
 
 
+_SIDE = {}
+
+
+def _side_streams(dev):
+    key = (dev.type, dev.index)
+    if key not in _SIDE:
+        _SIDE[key] = (torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev))
+    return _SIDE[key]
+
+
 def _adjacent(a, b):
     """True when ``b`` starts exactly where ``a`` ends inside the SAME storage (flat buffers)."""
     return (a.untyped_storage().data_ptr() == b.untyped_storage().data_ptr()
@@ -148,53 +158,68 @@ class _ICALstmFn(torch.autograd.Function):
             pairs["classifier.1"] = (hs["dz1"], hs["a0"])
             model._dad_pairs = pairs
 
+        # Independent pieces of the backward run on side streams (parallel branches when the step is
+        # captured in a CUDA graph): the transposes that do not depend on dP hide under the BPTT kernel
+        # (which occupies only 2 x H/32 SMs), and the three weight-gradient chains run side by side.
+        main = torch.cuda.current_stream(dev)
+        s1, s2 = _side_streams(dev)
+        if D == 2 and _adjacent(w_ih[0], w_ih[1]):
+            w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
+        else:
+            w_cat = torch.cat(w_ih, 0)
+        s1.wait_stream(main)
+        with torch.cuda.stream(s1):
+            HprevT = transpose_bf16(Hprev)          # [D*H,  S*B]
+            w_ihT = transpose_bf16(w_cat)           # [E, D*4H]
+            ev_side = torch.cuda.Event()
+            ev_side.record(s1)
+
         # 7. BPTT
         db_ih = [_grad_buf(c.i2h.bias) for c in cells]
         db_hh = [_grad_buf(c.h2h.bias) for c in cells]
         dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True)
+        ev_dp = torch.cuda.Event()
+        ev_dp.record(main)
 
         if capture:
             # LSTM pairs: delta = dP (per direction), activations = encoder output / previous hidden state
+            main.wait_event(ev_side)
             for dd in range(D):
                 sl = slice(dd * 4 * H, (dd + 1) * 4 * H)
                 model._dad_pairs[f"lstm.lstms.{dd}.i2h"] = (dP[:, sl], enc)
                 model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (dP[:, sl], Hprev[:, dd * H:(dd + 1) * H])
-            if D == 2 and _adjacent(w_ih[0], w_ih[1]):
-                w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
-            else:
-                w_cat = torch.cat(w_ih, 0)
-            w_ihT = transpose_bf16(w_cat)
             d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
             gemm_bf16(dP, w_ihT, out=d_enc, mask=enc)
             model._dad_pairs["encoder.0"] = (d_enc, xT.t())
             return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
-        # 8. K-major operands for the weight-gradient GEMMs
+        # branch A (s2): through the input projection and the encoder ReLU (bias gradient as column sums,
+        # result stored transposed = K-major operand of the next GEMM), then the encoder weights
+        BSp = (S * B + 7) // 8 * 8
+        s2.wait_event(ev_dp)
+        s2.wait_event(ev_side)
+        with torch.cuda.stream(s2):
+            d_encT = torch.empty(E, BSp, device=dev, dtype=torch.bfloat16)[:, :S * B]
+            gemm_bf16(dP, w_ihT, want_out=False, out_t=d_encT, mask=enc, colsum=_grad_buf(enc_l.bias))
+            gemm_bf16(d_encT, xT, out=_grad_buf(enc_l.weight), accumulate=True, split_k=0)
+        # main: K-major copy of dP, then the input-projection weights
         dPT = transpose_bf16(dP)                    # [D*4H, S*B]
-        HprevT = transpose_bf16(Hprev)              # [D*H,  S*B]
-        # 9. recurrent weights
-        for dd, c in enumerate(cells):
-            gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H], out=_grad_buf(c.h2h.weight),
-                      accumulate=True, split_k=0)
-        # 10. input-projection weights
+        ev_dpt = torch.cuda.Event()
+        ev_dpt.record(main)
+        # branch B (s1): recurrent weights
+        s1.wait_event(ev_dpt)
+        with torch.cuda.stream(s1):
+            for dd, c in enumerate(cells):
+                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H], out=_grad_buf(c.h2h.weight),
+                          accumulate=True, split_k=0)
         g_ih = [_grad_buf(c.i2h.weight) for c in cells]
         if D == 2 and _adjacent(g_ih[0], g_ih[1]):
             gemm_bf16(dPT, encT, out=_span(g_ih[0], (D * 4 * H, E), (E, 1)), accumulate=True, split_k=0)
         else:
             for dd in range(D):
                 gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], encT, out=g_ih[dd], accumulate=True, split_k=0)
-        # 11. through the input projection and the encoder ReLU; bias gradient as column sums;
-        #     result stored transposed (K-major operand of the encoder weight gradient)
-        if D == 2 and _adjacent(w_ih[0], w_ih[1]):
-            w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
-        else:
-            w_cat = torch.cat(w_ih, 0)
-        w_ihT = transpose_bf16(w_cat)               # [E, D*4H]
-        BSp = (S * B + 7) // 8 * 8
-        d_encT = torch.empty(E, BSp, device=dev, dtype=torch.bfloat16)[:, :S * B]
-        gemm_bf16(dP, w_ihT, want_out=False, out_t=d_encT, mask=enc, colsum=_grad_buf(enc_l.bias))
-        # 12. encoder weights
-        gemm_bf16(d_encT, xT, out=_grad_buf(enc_l.weight), accumulate=True, split_k=0)
+        main.wait_stream(s1)
+        main.wait_stream(s2)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 
