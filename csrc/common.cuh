@@ -174,6 +174,17 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
     return d;
 }
 
+// K-major operand WITHOUT swizzle ("interleaved" canonical layout): 8-row x 16-byte core matrices,
+// lbo = byte distance between core matrices adjacent in K, sbo = between 8-row groups.
+__device__ __forceinline__ uint64_t umma_desc_k_noswizzle(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;            // descriptor version (Blackwell); layout type 0 = no swizzle
+    return d;
+}
+
 // Instruction descriptor for kind::f16: bf16 x bf16 -> fp32, both operands K-major.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
     return (1u << 4)                       // c_format = F32

@@ -13,19 +13,23 @@
 //
 // forward, per step (all-gather design):
 //   tcgen05.mma  D[128 gate rows, 16 batch] = W_hh[own rows, 0:H] · h_{t-1}[batch, 0:H]ᵀ
-//                (A = weight slice, K-major SW128 smem; B = h_{t-1} in smem, every CTA holds
-//                the full vector; accumulator in TMEM)
+//                (A = weight slice, K-major SW128 smem; B = h_{t-1}, K-major un-swizzled smem, every
+//                CTA holds the full vector; accumulator in TMEM; issued under elect.sync)
 //   epilogue     tcgen05.ld → + i2h(x_t) + b_hh → σ(σ(·)) / tanh → cell update in registers →
-//                h_t slice (bf16) is stored straight into EVERY cluster CTA's next-step B operand
-//                through distributed shared memory → barrier.cluster.
+//                the CTA's h_t slice (bf16, two contiguous 512-byte runs in the operand layout) is
+//                staged and pushed into EVERY cluster CTA's next-step B operand with cp.async.bulk
+//                (shared::cta → shared::cluster); each copy does one complete_tx on the receiver's
+//                mbarrier, whose completion releases the receiver's next MMA.  No cluster barrier and
+//                no proxy fence between CTAs on the critical path.
 // backward, per step (reduce-scatter design):
 //   tcgen05.mma  partial dh[H units, 16 batch] = W_hhᵀ[0:H, own gate rows] · dP_t[batch, own rows]ᵀ
 //                (K = this CTA's 128 gate rows, so the B operand is purely local)
-//   exchange     each warp ships its 32-unit block of the partial to the CTA that owns those
-//                units (DSMEM) → barrier.cluster → owner sums the H/32 partials, adds the
-//                upstream gradient, back-propagates through the cell and the double sigmoid,
-//                emits dP_{t-1} (bf16, to global for the weight-gradient GEMMs and to its local B
-//                operand for the next step).
+//   exchange     each warp stages its 32-unit block of the partial (2 KB) and bulk-copies it to the
+//                CTA that owns those units → that CTA's mbarrier completes when all H/32 blocks have
+//                landed → owner sums them, adds the upstream gradient, back-propagates through the cell
+//                and the double sigmoid, emits dP_{t-1} (bf16: to global memory for the weight-gradient
+//                GEMMs, and to its local B operand for the next step).
+// Global loads for step t±1 and the global stores of step t∓1 are software-pipelined around the MMA.
 // Activations use tanh.approx (one MUFU op per sigmoid/tanh).
 #include "common.cuh"
 #include "../include/dinunet_b200.h"
@@ -83,6 +87,8 @@ __device__ __forceinline__ float dsig(float y) { return y * (1.f - y); }
 // 64-wide k-blocks: A blocks are 128 rows (16 KB) apart, B blocks NB rows (2 KB) apart
 __device__ __forceinline__ constexpr uint64_t koff_a(int k) { return (uint64_t)((k >> 2) * (128 * 128 / 16) + (k & 3) * 2); }
 __device__ __forceinline__ constexpr uint64_t koff_b(int k) { return (uint64_t)((k >> 2) * (NB * 128 / 16) + (k & 3) * 2); }
+// forward B operand (h_{t-1}) is stored without swizzle: one K=16 step = two 128-byte core matrices
+__device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(k * (256 / 16)); }
 
 // ------------------------------------------------------------------------------------ forward
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
@@ -90,11 +96,17 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
     const int H = a.H, KB = (H + 63) / 64;           // k-blocks of the recurrent GEMM
     const int a_bytes = KB * 128 * 128;              // weight slice: 128 rows x (KB*64) k
-    const int h_bytes = KB * NB * 128;               // one h buffer
+    // h_{t-1} as the MMA B operand: K-major, NO swizzle — 8-row x 16-byte core matrices, consecutive
+    // k-chunks 128 B apart, the two 8-row groups h_sbo apart.  In this layout the 32 hidden units a CTA
+    // produces are two contiguous 512-byte runs (one per row group), so a CTA hands its slice to a peer
+    // with two bulk copies instead of 64 per-thread 16-byte stores.
+    const int h_sbo = (H / 8) * 128;                 // bytes between the two 8-row groups
+    const int h_bytes = NB * H * 2;                  // one h buffer (= 2 * h_sbo)
     uint8_t* sA = smem;
     uint8_t* sH = smem + a_bytes;                    // two buffers
     float* sAct = reinterpret_cast<float*>(sH + 2 * h_bytes);   // [4][NB][U]
-    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sAct + 4 * NB * U);
+    uint8_t* sStage = reinterpret_cast<uint8_t*>(sAct + 4 * NB * U);   // [2 parity][2 row groups][512 B] own h slice
+    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStage + 2 * 1024);
     uint64_t* hbar = mma_bar + 1;                    // [2]: "h_{t-1} has fully arrived in buffer p"
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(hbar + 2);
 
@@ -183,13 +195,15 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     // broadcast from lane 0 so the compiler keeps descriptors / TMEM address in uniform registers
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t da_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sA), 0));
-    const uint64_t db_base0 = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sH), 0));
-    const uint64_t db_base1 = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sH + h_bytes), 0));
+    const uint32_t sH_u = __shfl_sync(0xffffffffu, dnb::smem_u32(sH), 0);
+    const uint64_t db_base0 = dnb::umma_desc_k_noswizzle(sH_u, 128, h_sbo);
+    const uint64_t db_base1 = dnb::umma_desc_k_noswizzle(sH_u + h_bytes, 128, h_sbo);
     const int ksteps = H / 16;
-    // destination of this thread's 16-byte h chunk (even ug lanes send): same offset in every CTA
-    const uint32_t chunk_off = sw128_off(NB, b2, cta * U + (ug & ~1) * 4);
-    const uint32_t send_data[2] = {dnb::smem_u32(sH) + chunk_off, dnb::smem_u32(sH + h_bytes) + chunk_off};
-    const uint32_t send_bar[2] = {dnb::smem_u32(&hbar[0]), dnb::smem_u32(&hbar[1])};
+    // this thread's 8 bytes (4 units of batch row b2) inside the staged slice: [row group][k-chunk][row][16 B]
+    const uint32_t stage_off = (uint32_t)((b2 >> 3) * 512 + (ug >> 1) * 128 + (b2 & 7) * 16 + (ug & 1) * 8);
+    const uint32_t sStage_u = __shfl_sync(0xffffffffu, dnb::smem_u32(sStage), 0);
+    const uint32_t hbar_u = __shfl_sync(0xffffffffu, dnb::smem_u32(&hbar[0]), 0);
+    const uint32_t slice_off = (uint32_t)(cta * 4 * 128);     // where this CTA's 4 k-chunks sit inside a row group
 
     // Software pipeline: i2h(x) for step t+1 is fetched during step t; the global stores of step t
     // (saved pre-activations, cell state, h for the weight-gradient GEMM) are issued at the start of
@@ -219,7 +233,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
                 if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
 #pragma unroll
                 for (int k = 0; k < 16; ++k)
-                    if (k < ksteps) dnb::umma_bf16_ss(tmem_u, da_base + koff_a(k), db_base + koff_b(k), idesc, k != 0);
+                    if (k < ksteps) dnb::umma_bf16_ss(tmem_u, da_base + koff_a(k), db_base + koff_h(k), idesc, k != 0);
                 dnb::umma_commit(mma_bar);
             }
             __syncwarp();
@@ -284,25 +298,32 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         hb.y = dnb::pack_bf16x2(hlast[2], hlast[3]);
         hb_prev = hb;
         if (t + 1 < a.S) {
-            // pair two lanes into one 16-byte swizzle chunk; st.async drops it into every CTA's next
-            // B operand and counts 16 bytes on that CTA's "h arrived" barrier
-            uint2 other;
-            other.x = __shfl_xor_sync(0xffffffffu, hb.x, 1);
-            other.y = __shfl_xor_sync(0xffffffffu, hb.y, 1);
-            if ((ug & 1) == 0) {
-                const uint4 chunk = make_uint4(hb.x, hb.y, other.x, other.y);
-                const uint32_t d_off = send_data[(t + 1) & 1], b_off = send_bar[(t + 1) & 1];
+            // stage the slice, then (one elected thread) two 512-byte bulk copies per peer: data lands in
+            // every CTA's next B operand and counts on that CTA's "h arrived" barrier (async proxy on both
+            // ends: no cluster barrier, and one mbarrier update per copy instead of one per 16 bytes)
+            const int par = (t + 1) & 1;
+            *reinterpret_cast<uint2*>(sStage + par * 1024 + stage_off) = hb;
+            dnb::fence_proxy_async_smem();
+            __syncthreads();
+            if (dnb::elect_one()) {                       // one thread per warp; warp w serves peers w, w+4
+                const uint32_t src = sStage_u + par * 1024;
+                const uint32_t dst = sH_u + par * h_bytes + slice_off;
+                const uint32_t bar = hbar_u + par * 8;
 #pragma unroll
-                for (int peer = 0; peer < kMaxCtas; ++peer)
-                    if (peer < ncta) dnb::st_async_v4(dnb::mapa(d_off, peer), chunk, dnb::mapa(b_off, peer));
+                for (int pp = 0; pp < kMaxCtas / 4; ++pp) {
+                    const int peer = warp + 4 * pp;
+                    if (peer < ncta) {
+                        const uint32_t rbar = dnb::mapa(bar, peer);
+                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(dst, peer), src, 512, rbar);
+                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(dst + h_sbo, peer), src + 512, 512, rbar);
+                    }
+                }
             }
         }
         DNB_STAMP(7);
         px_ptr += px_step;
         c_ptr += c_step;
         hp_ptr += hp_step;
-        // No block barrier here: sAct is rewritten only after the next MMA completes, and that MMA
-        // is issued only after every thread of this CTA has sent its h chunk (i.e. finished reading).
         DNB_STAMP(8);
         DNB_STAMP(9);
     }
@@ -676,7 +697,7 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
     const int ncta = d->H / U, KB = (d->H + 63) / 64;
-    const size_t smem = (size_t)KB * 128 * 128 + 2 * (size_t)KB * NB * 128 + 4 * NB * U * 4 + 128 + 1024;
+    const size_t smem = (size_t)KB * 128 * 128 + 2 * (size_t)NB * d->H * 2 + 4 * NB * U * 4 + 2 * 1024 + 128 + 1024;
     const int tiles = (d->B + NB - 1) / NB;
     return launch_cluster(lstm_fwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }
