@@ -2,16 +2,17 @@
 //
 // Reference: comps/icalstm/models.py:95-103 —
 //   Dropout(.25) -> Linear(N0,N1) -> BatchNorm1d(N1) -> ReLU -> Linear(N1,N2) -> ReLU -> Linear(N2,N3)
-// with N0 = hidden (384), N1 = 256, N2 = 64, N3 = classes, batch 16-64.  Everything here is
-// latency-bound small-matrix work (M = batch), far below a tcgen05 tile, and it sits on the
-// serial chain LSTM -> head -> loss -> head' -> LSTM'.  So the layers are spread over many CTAs
-// with warp-level dot products (lanes split K with 16-byte bf16 weight loads, shuffle reduce) and
-// the BatchNorm statistics — per feature over the batch — are computed by the warp that owns the
-// feature, with no extra pass:
-//   forward  : [16 CTAs] Linear1 + BN + ReLU      ->  [1 CTA] Linear2 + ReLU + Linear3
-//   backward : [1 CTA] layers 3, 2 and BN         ->  [38 CTAs] dW1 (feature tiles) and dx (column tiles)
-// Weights are read as bf16 (the parameter shadow); accumulation, saved activations and all
-// gradients are fp32.  Parameter gradients are accumulated (+=) when `accumulate` is set.
+// with N0 = hidden (384), N1 = 256, N2 = 64, N3 = classes, batch 16-64.  This is latency-bound
+// small-matrix work (M = batch) on the serial chain LSTM -> head -> loss -> head' -> LSTM', and every
+// kernel runs once per step, so what matters is (a) many warps in flight and (b) few instructions per
+// warp (a long unrolled instruction stream executed once by 8 warps costs ~6 cycles per instruction:
+// the first versions spent 20-30 us per launch that way).  Hence: ONE output element per thread with a
+// short loop over K, 16 consecutive lanes = 16 batch rows of one feature, so BatchNorm's per-feature
+// batch statistics are 16-lane shuffle reductions.
+//   forward  : [N1/8 CTAs] Linear1 + BN + ReLU        -> [N2/16 CTAs] Linear2 + ReLU + partial Linear3
+//   backward : [N1/16 CTAs] layers 3, 2 and BN         -> [N1/8 + N0/16 CTAs] dW1 and dx
+// Weights are read as bf16 (the parameter shadow); accumulation, saved activations and all gradients
+// are fp32.  Parameter gradients are accumulated (+=, fire-and-forget RED) when `accumulate` is set.
 #include "common.cuh"
 #include "../include/dinunet_b200.h"
 
@@ -21,9 +22,8 @@ void dnb_count_launch(int n);
 
 namespace {
 
-constexpr int BT = 16;          // batch rows handled per register tile
-constexpr int FPW = 4;          // features per warp
-constexpr int kMaxB = 64;
+constexpr int kMaxB = 64;        // batch rows supported (4 chunks of 16 lanes)
+constexpr int kChunks = kMaxB / 16;
 
 struct HeadFwdArgs {
     const float* x; const float* drop;
@@ -46,277 +46,259 @@ struct HeadBwdArgs {
     int B, N0, N1, N2, N3;
 };
 
-__device__ __forceinline__ void put(float* p, float v, int acc) { *p = acc ? (*p + v) : v; }
-
-__device__ __forceinline__ void bf16x8_to_f32(const uint4& raw, float (&w)[8]) {
-    const uint32_t u[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        w[2 * i] = __uint_as_float(u[i] << 16);
-        w[2 * i + 1] = __uint_as_float(u[i] & 0xFFFF0000u);
-    }
+// accumulate with a fire-and-forget RED (no load -> no L2 round trip on the critical path)
+__device__ __forceinline__ void put(float* p, float v, int acc) {
+    if (acc) atomicAdd(p, v);
+    else *p = v;
 }
 
-// One warp: dot products of FPW weight rows (bf16, row pitch ldw) with BT activation rows held in
-// shared memory (fp32, row pitch K).  Lanes split K in 8-element chunks; result summed over the
-// warp, every lane ends up with all FPW x BT sums.
-__device__ __forceinline__ void warp_dots(const __nv_bfloat16* __restrict__ W, int ldw, int nfeat, const float* xs,
-                                          int K, int b0, int B, float (&acc)[FPW][BT]) {
-    const int lane = threadIdx.x & 31;
+// sum over the 16 lanes that share a feature (xor offsets < 16 stay inside a half-warp)
+__device__ __forceinline__ float sum16(float v) {
 #pragma unroll
-    for (int f = 0; f < FPW; ++f)
-#pragma unroll
-        for (int b = 0; b < BT; ++b) acc[f][b] = 0.f;
-    for (int c = lane; c < K / 8; c += 32) {
-        float w[FPW][8];
-#pragma unroll
-        for (int f = 0; f < FPW; ++f) {
-            if (f < nfeat) bf16x8_to_f32(*reinterpret_cast<const uint4*>(W + (size_t)f * ldw + c * 8), w[f]);
-            else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) w[f][i] = 0.f;
-            }
-        }
-#pragma unroll
-        for (int b = 0; b < BT; ++b) {
-            if (b0 + b < B) {
-                const float4 x0 = *reinterpret_cast<const float4*>(xs + (size_t)(b0 + b) * K + c * 8);
-                const float4 x1 = *reinterpret_cast<const float4*>(xs + (size_t)(b0 + b) * K + c * 8 + 4);
-#pragma unroll
-                for (int f = 0; f < FPW; ++f)
-                    acc[f][b] += w[f][0] * x0.x + w[f][1] * x0.y + w[f][2] * x0.z + w[f][3] * x0.w + w[f][4] * x1.x +
-                                 w[f][5] * x1.y + w[f][6] * x1.z + w[f][7] * x1.w;
-            }
-        }
-    }
-#pragma unroll
-    for (int f = 0; f < FPW; ++f)
-#pragma unroll
-        for (int b = 0; b < BT; ++b) acc[f][b] = dnb::warp_sum(acc[f][b]);
+    for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float dot8(const uint4& w, const float4& x0, const float4& x1) {
+    return __uint_as_float(w.x << 16) * x0.x + __uint_as_float(w.x & 0xFFFF0000u) * x0.y +
+           __uint_as_float(w.y << 16) * x0.z + __uint_as_float(w.y & 0xFFFF0000u) * x0.w +
+           __uint_as_float(w.z << 16) * x1.x + __uint_as_float(w.z & 0xFFFF0000u) * x1.y +
+           __uint_as_float(w.w << 16) * x1.z + __uint_as_float(w.w & 0xFFFF0000u) * x1.w;
 }
 
 // ------------------------------------------------------------------ forward, launch 1: Linear1 + BN + ReLU
-constexpr int kL1Warps = 4;
-__global__ void __launch_bounds__(kL1Warps * 32) head_l1_kernel(const HeadFwdArgs a) {
+// CTA = 8 features x 16 lanes.  Thread (f, l) owns batch rows l, l+16, ... of feature f.
+constexpr int kF1Feat = 8;
+constexpr int kF1Threads = kF1Feat * 16;
+__global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a) {
     extern __shared__ float sm[];
-    float* xs = sm;                                   // [B][N0] dropped input
-    float* zs = xs + a.B * a.N0;                      // [warps][FPW][kMaxB] pre-BN values
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, B = a.B;
+    const int B = a.B, N0 = a.N0, ldx = N0 + 4;       // +4 floats: rows of different lanes land in different banks
+    float* xs = sm;                                    // [B][ldx] dropped input
+    const int tid = threadIdx.x, f = tid >> 4, l = tid & 15;
     {
-        // vectorised, unrolled staging: independent 16-byte loads in flight instead of a dependent chain
-        const int n4 = B * a.N0 / 4;
+        const int per_row = N0 / 4;
         const float4* x4 = reinterpret_cast<const float4*>(a.x);
         const float4* d4 = reinterpret_cast<const float4*>(a.drop);
 #pragma unroll 4
-        for (int i = tid; i < n4; i += kL1Warps * 32) {
+        for (int i = tid; i < B * per_row; i += kF1Threads) {
             float4 v = x4[i];
             if (d4) {
                 const float4 d = d4[i];
                 v.x *= d.x; v.y *= d.y; v.z *= d.z; v.w *= d.w;
             }
-            reinterpret_cast<float4*>(xs)[i] = v;
+            const int r = i / per_row, c = i % per_row;
+            *reinterpret_cast<float4*>(xs + r * ldx + c * 4) = v;
             if (a.a0 && blockIdx.x == 0) reinterpret_cast<float4*>(a.a0)[i] = v;
         }
+        if (blockIdx.x == 0)                           // Linear3 accumulates into logits in launch 2: start from the bias
+            for (int i = tid; i < B * a.N3; i += kF1Threads) a.logits[i] = a.b3[i % a.N3];
     }
     __syncthreads();
-    const int j0 = (blockIdx.x * kL1Warps + warp) * FPW;
-    if (j0 >= a.N1) return;
-    const int nfeat = min(FPW, a.N1 - j0);
-    float* z = zs + warp * FPW * kMaxB;
-    for (int b0 = 0; b0 < B; b0 += BT) {
-        float acc[FPW][BT];
-        warp_dots(a.W1 + (size_t)j0 * a.N0, a.N0, nfeat, xs, a.N0, b0, B, acc);
+    const int j = blockIdx.x * kF1Feat + f;
+    if (j >= a.N1) return;
+    const uint4* w = reinterpret_cast<const uint4*>(a.W1 + (size_t)j * N0);
+    float z[kChunks];
 #pragma unroll
-        for (int f = 0; f < FPW; ++f)
+    for (int c = 0; c < kChunks; ++c) z[c] = 0.f;
 #pragma unroll
-            for (int b = 0; b < BT; ++b)
-                if (lane == b && b0 + b < B) z[f * kMaxB + b0 + b] = acc[f][b];
+    for (int c = 0; c < kChunks; ++c) {
+        if (c * 16 < B) {
+            const int b = c * 16 + l;
+            const float* xr = xs + (b < B ? b : 0) * ldx;
+            float acc = 0.f;
+#pragma unroll 4
+            for (int k = 0; k < N0 / 8; ++k)
+                acc += dot8(w[k], *reinterpret_cast<const float4*>(xr + k * 8),
+                            *reinterpret_cast<const float4*>(xr + k * 8 + 4));
+            z[c] = b < B ? acc + a.b1[j] : 0.f;
+        }
     }
-    __syncwarp();
-    for (int f = 0; f < nfeat; ++f) {
-        const int j = j0 + f;
-        const float bias = a.b1[j];
-        float v0 = lane < B ? z[f * kMaxB + lane] + bias : 0.f;
-        float v1 = lane + 32 < B ? z[f * kMaxB + lane + 32] + bias : 0.f;
-        const float mean = dnb::warp_sum(v0 + v1) / (float)B;
-        const float d0 = lane < B ? v0 - mean : 0.f, d1 = lane + 32 < B ? v1 - mean : 0.f;
-        const float var = dnb::warp_sum(d0 * d0 + d1 * d1) / (float)B;
-        float use_mean = mean, use_var = var;
-        if (a.training) {
-            if (a.run_mean && lane == 0) {
-                a.run_mean[j] = (1.f - a.momentum) * a.run_mean[j] + a.momentum * mean;
-                const float unbiased = B > 1 ? var * (float)B / (float)(B - 1) : var;
-                a.run_var[j] = (1.f - a.momentum) * a.run_var[j] + a.momentum * unbiased;
-            }
-        } else {
-            use_mean = a.run_mean[j];
-            use_var = a.run_var[j];
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) s += z[c];
+    const float mean = sum16(s) / (float)B;
+    float q = 0.f;
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) q += (c * 16 + l < B) ? (z[c] - mean) * (z[c] - mean) : 0.f;
+    const float var = sum16(q) / (float)B;
+    float use_mean = mean, use_var = var;
+    if (a.training) {
+        if (a.run_mean && l == 0) {
+            a.run_mean[j] = (1.f - a.momentum) * a.run_mean[j] + a.momentum * mean;
+            a.run_var[j] = (1.f - a.momentum) * a.run_var[j] + a.momentum * (B > 1 ? var * (float)B / (float)(B - 1) : var);
         }
-        const float istd = rsqrtf(use_var + a.eps);
-        if (lane == 0) a.invstd[j] = istd;
-        const float g = a.bn_w[j], be = a.bn_b[j];
-        if (lane < B) {
-            const float xh = (v0 - use_mean) * istd;
-            a.xhat[lane * a.N1 + j] = xh;
-            a.a1[lane * a.N1 + j] = fmaxf(xh * g + be, 0.f);
-        }
-        if (lane + 32 < B) {
-            const float xh = (v1 - use_mean) * istd;
-            a.xhat[(lane + 32) * a.N1 + j] = xh;
-            a.a1[(lane + 32) * a.N1 + j] = fmaxf(xh * g + be, 0.f);
+    } else {
+        use_mean = a.run_mean[j];
+        use_var = a.run_var[j];
+    }
+    const float istd = rsqrtf(use_var + a.eps);
+    if (l == 0) a.invstd[j] = istd;
+    const float g = a.bn_w[j], be = a.bn_b[j];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) {
+        const int b = c * 16 + l;
+        if (b < B) {
+            const float xh = (z[c] - use_mean) * istd;
+            a.xhat[b * a.N1 + j] = xh;
+            a.a1[b * a.N1 + j] = fmaxf(xh * g + be, 0.f);
         }
     }
 }
 
 // ------------------------------------------------------------------ forward, launch 2: Linear2 + ReLU + Linear3
-constexpr int kL23Threads = 256;
-__global__ void __launch_bounds__(kL23Threads) head_l23_kernel(const HeadFwdArgs a) {
+// CTA = 16 features of layer 2 x 16 lanes; Linear3 is accumulated into `logits` (preset to b3 by
+// launch 1) with one atomic per (row, class, CTA).
+constexpr int kF2Feat = 16;
+constexpr int kF2Threads = kF2Feat * 16;
+__global__ void __launch_bounds__(kF2Threads) head_f2_kernel(const HeadFwdArgs a) {
     extern __shared__ float sm[];
-    float* s1 = sm;                       // [B][N1]
-    float* s2 = s1 + a.B * a.N1;          // [B][N2]
-    float* s3 = s2 + a.B * a.N2;          // [N3][N2] last-layer weights
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, B = a.B;
+    const int B = a.B, N1 = a.N1, N2 = a.N2, N3 = a.N3, lda = N1 + 4;
+    float* s1 = sm;                        // [B][lda] layer-1 activations
+    float* s2 = s1 + B * lda;              // [B][kF2Feat] this CTA's layer-2 activations
+    const int tid = threadIdx.x, f = tid >> 4, l = tid & 15;
     {
-        const int n4 = B * a.N1 / 4;
+        const int per_row = N1 / 4;
         const float4* src = reinterpret_cast<const float4*>(a.a1);
 #pragma unroll 4
-        for (int i = tid; i < n4; i += kL23Threads) reinterpret_cast<float4*>(s1)[i] = src[i];
-#pragma unroll 2
-        for (int i = tid; i < a.N3 * a.N2; i += kL23Threads) s3[i] = __bfloat162float(a.W3[i]);
-    }
-    __syncthreads();
-    for (int j0 = warp * FPW; j0 < a.N2; j0 += (kL23Threads / 32) * FPW) {
-        const int nfeat = min(FPW, a.N2 - j0);
-        for (int b0 = 0; b0 < B; b0 += BT) {
-            float acc[FPW][BT];
-            warp_dots(a.W2 + (size_t)j0 * a.N1, a.N1, nfeat, s1, a.N1, b0, B, acc);
-#pragma unroll
-            for (int f = 0; f < FPW; ++f)
-#pragma unroll
-                for (int b = 0; b < BT; ++b)
-                    if (lane == b && f < nfeat && b0 + b < B) {
-                        const float v = fmaxf(acc[f][b] + a.b2[j0 + f], 0.f);
-                        s2[(b0 + b) * a.N2 + j0 + f] = v;
-                        a.a2[(b0 + b) * a.N2 + j0 + f] = v;
-                    }
+        for (int i = tid; i < B * per_row; i += kF2Threads) {
+            const int r = i / per_row, c = i % per_row;
+            *reinterpret_cast<float4*>(s1 + r * lda + c * 4) = src[i];
         }
     }
     __syncthreads();
-    for (int idx = tid; idx < B * a.N3; idx += kL23Threads) {
-        const int b = idx / a.N3, c = idx % a.N3;
-        const float* w = s3 + c * a.N2;
-        float acc = a.b3[c];
-#pragma unroll 8
-        for (int k = 0; k < a.N2; ++k) acc += w[k] * s2[b * a.N2 + k];
-        a.logits[idx] = acc;
+    const int j0 = blockIdx.x * kF2Feat, j = j0 + f;
+    if (j < N2) {
+        const uint4* w = reinterpret_cast<const uint4*>(a.W2 + (size_t)j * N1);
+        const float bias = a.b2[j];
+#pragma unroll 1
+        for (int c = 0; c * 16 < B; ++c) {
+            const int b = c * 16 + l;
+            const float* xr = s1 + (b < B ? b : 0) * lda;
+            float acc = 0.f;
+#pragma unroll 4
+            for (int k = 0; k < N1 / 8; ++k)
+                acc += dot8(w[k], *reinterpret_cast<const float4*>(xr + k * 8),
+                            *reinterpret_cast<const float4*>(xr + k * 8 + 4));
+            if (b < B) {
+                const float v = fmaxf(acc + bias, 0.f);
+                s2[b * kF2Feat + f] = v;
+                a.a2[b * N2 + j] = v;
+            }
+        }
+    }
+    __syncthreads();
+    const int nf = min(kF2Feat, N2 - j0);
+    for (int idx = tid; idx < B * N3; idx += kF2Threads) {
+        const int b = idx / N3, c = idx % N3;
+        float acc = 0.f;
+        for (int k = 0; k < nf; ++k) acc += __bfloat162float(a.W3[(size_t)c * N2 + j0 + k]) * s2[b * kF2Feat + k];
+        atomicAdd(a.logits + idx, acc);
     }
 }
 
-// ------------------------------------------------------------------ backward, launch 1: layers 3, 2 and BN
-constexpr int kB23Threads = 256;
-template <int BTT>
-__global__ void __launch_bounds__(kB23Threads, 1) head_bwd_l23_kernel(const HeadBwdArgs a) {
+// ------------------------------------------------------------------ backward, launch 1: layers 3, 2 and BatchNorm
+// CTA = 16 features of layer 1 x 16 lanes (batch).  Every CTA rebuilds the tiny dz2 = dL/d(pre-ReLU2)
+// [B, N2] in shared memory; CTA 0 also produces the layer-3 / bias-2 gradients.  Zeroes dx for launch 2.
+constexpr int kB1Feat = 16;
+constexpr int kB1Threads = kB1Feat * 16;
+__global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a) {
     extern __shared__ float sm[];
-    const int B = a.B, N1 = a.N1, N2 = a.N2, N3 = a.N3, tid = threadIdx.x, acc_mode = a.accumulate;
+    const int B = a.B, N0 = a.N0, N1 = a.N1, N2 = a.N2, N3 = a.N3, acc_mode = a.accumulate;
+    const int ldz = N2 + 1;
     float* sdl = sm;                       // [B][N3]
-    float* sa2 = sdl + B * N3;             // [B][N2]
-    float* sdz2 = sa2 + B * N2;            // [B][N2]
-    float* sw3 = sdz2 + B * N2;            // [N3][N2]
-    for (int i = tid; i < B * N3; i += kB23Threads) sdl[i] = a.dlogits[i];
-#pragma unroll 4
-    for (int i = tid; i < B * N2; i += kB23Threads) sa2[i] = a.a2[i];
-    for (int i = tid; i < N3 * N2; i += kB23Threads) sw3[i] = __bfloat162float(a.W3[i]);
+    float* sdz2 = sdl + B * N3;            // [B][ldz]
+    float* sa1 = sdz2 + B * ldz;           // [B][kB1Feat] this CTA's layer-1 activations
+    const int tid = threadIdx.x, f = tid >> 4, l = tid & 15;
+    for (int i = tid; i < B * N3; i += kB1Threads) sdl[i] = a.dlogits[i];
+    for (int i = blockIdx.x * kB1Threads + tid; i < B * N0; i += gridDim.x * kB1Threads) a.dx[i] = 0.f;
     __syncthreads();
-    for (int idx = tid; idx < N3 * N2; idx += kB23Threads) {
-        const int c = idx / N2, k = idx % N2;
-        float s = 0.f;
-        for (int b = 0; b < B; ++b) s += sdl[b * N3 + c] * sa2[b * N2 + k];
-        put(a.dW3 + idx, s, acc_mode);
-    }
-    for (int c = tid; c < N3; c += kB23Threads) {
-        float s = 0.f;
-        for (int b = 0; b < B; ++b) s += sdl[b * N3 + c];
-        put(a.db3 + c, s, acc_mode);
-    }
-    for (int idx = tid; idx < B * N2; idx += kB23Threads) {
+    for (int idx = tid; idx < B * N2; idx += kB1Threads) {
         const int b = idx / N2, k = idx % N2;
         float s = 0.f;
-        for (int c = 0; c < N3; ++c) s += sdl[b * N3 + c] * sw3[c * N2 + k];
-        sdz2[idx] = sa2[idx] > 0.f ? s : 0.f;
+        for (int c = 0; c < N3; ++c) s += sdl[b * N3 + c] * __bfloat162float(a.W3[c * N2 + k]);
+        sdz2[b * ldz + k] = a.a2[idx] > 0.f ? s : 0.f;
     }
     __syncthreads();
-    for (int k = tid; k < N2; k += kB23Threads) {
-        float s = 0.f;
-        for (int b = 0; b < B; ++b) s += sdz2[b * N2 + k];
-        put(a.db2 + k, s, acc_mode);
+    if (blockIdx.x == 0) {
+        for (int idx = tid; idx < N3 * N2; idx += kB1Threads) {
+            const int c = idx / N2, k = idx % N2;
+            float s = 0.f;
+            for (int b = 0; b < B; ++b) s += sdl[b * N3 + c] * a.a2[b * N2 + k];
+            put(a.dW3 + idx, s, acc_mode);
+        }
+        for (int c = tid; c < N3; c += kB1Threads) {
+            float s = 0.f;
+            for (int b = 0; b < B; ++b) s += sdl[b * N3 + c];
+            put(a.db3 + c, s, acc_mode);
+        }
+        for (int k = tid; k < N2; k += kB1Threads) {
+            float s = 0.f;
+            for (int b = 0; b < B; ++b) s += sdz2[b * ldz + k];
+            put(a.db2 + k, s, acc_mode);
+        }
     }
-    // thread = feature j of N1: all batch rows in registers -> BN backward needs no reduction
-    for (int j = tid; j < N1; j += kB23Threads) {
-        float a1r[BTT], xh[BTT], da1[BTT];
+    const int j0 = blockIdx.x * kB1Feat, j = j0 + f;     // N1 % 16 == 0: every thread has a valid feature
+    float dy[kChunks], xh[kChunks];
+    float sg = 0.f, sb = 0.f;
 #pragma unroll
-        for (int b = 0; b < BTT; ++b) {
-            a1r[b] = b < B ? a.a1[b * N1 + j] : 0.f;
-            xh[b] = b < B ? a.xhat[b * N1 + j] : 0.f;
-            da1[b] = 0.f;
+    for (int c = 0; c < kChunks; ++c) {
+        dy[c] = 0.f;
+        xh[c] = 0.f;
+        if (c * 16 < B) {
+            const int b = c * 16 + l;
+            const bool ok = b < B;
+            const float* dz = sdz2 + (ok ? b : 0) * ldz;
+            float acc = 0.f;
+#pragma unroll 8
+            for (int k = 0; k < N2; ++k) acc += dz[k] * __bfloat162float(a.W2[(size_t)k * N1 + j]);
+            const float a1v = ok ? a.a1[b * N1 + j] : 0.f;
+            if (ok) sa1[b * kB1Feat + f] = a1v;
+            xh[c] = ok ? a.xhat[b * N1 + j] : 0.f;
+            dy[c] = (ok && a1v > 0.f) ? acc : 0.f;
+            sg += dy[c] * xh[c];
+            sb += dy[c];
         }
-        for (int k0 = 0; k0 < N2; k0 += 8) {
-            float w8[8], old8[8];
+    }
+    const float dgamma = sum16(sg), dbeta = sum16(sb);
+    const float gi = a.bn_w[j] * a.invstd[j], invB = 1.f / (float)B;
+    float s1 = 0.f;
 #pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {              // 8 independent loads per trip
-                const int k = k0 + kk;
-                w8[kk] = k < N2 ? __bfloat162float(a.W2[(size_t)k * N1 + j]) : 0.f;
-                old8[kk] = (acc_mode && k < N2) ? a.dW2[(size_t)k * N1 + j] : 0.f;
-            }
-#pragma unroll
-            for (int kk = 0; kk < 8; ++kk) {
-                const int k = k0 + kk;
-                if (k < N2) {
-                    float s = 0.f;
-#pragma unroll
-                    for (int b = 0; b < BTT; ++b)
-                        if (b < B) {
-                            const float dz = sdz2[b * N2 + k];
-                            s += dz * a1r[b];
-                            da1[b] += dz * w8[kk];
-                        }
-                    a.dW2[(size_t)k * N1 + j] = old8[kk] + s;
-                }
-            }
+    for (int c = 0; c < kChunks; ++c) {
+        const int b = c * 16 + l;
+        if (b < B) {
+            const float dz = a.training ? gi * (dy[c] - dbeta * invB - xh[c] * dgamma * invB) : gi * dy[c];
+            a.dz1[b * N1 + j] = dz;
+            s1 += dz;
         }
-        float dgamma = 0.f, dbeta = 0.f;
-#pragma unroll
-        for (int b = 0; b < BTT; ++b)
-            if (b < B) {
-                const float dy = a1r[b] > 0.f ? da1[b] : 0.f;
-                da1[b] = dy;
-                dgamma += dy * xh[b];
-                dbeta += dy;
-            }
+    }
+    s1 = sum16(s1);
+    if (l == 0) {
         put(a.dbn_w + j, dgamma, acc_mode);
         put(a.dbn_b + j, dbeta, acc_mode);
-        const float gi = a.bn_w[j] * a.invstd[j];
-        const float invB = 1.f / (float)B;
-        float db1 = 0.f;
-#pragma unroll
-        for (int b = 0; b < BTT; ++b)
-            if (b < B) {
-                const float dz = a.training ? gi * (da1[b] - dbeta * invB - xh[b] * dgamma * invB) : gi * da1[b];
-                a.dz1[b * N1 + j] = dz;
-                db1 += dz;
-            }
-        put(a.db1 + j, db1, acc_mode);
+        put(a.db1 + j, s1, acc_mode);
+    }
+    __syncthreads();
+    // dW2[k][j0..j0+15] (+)= sum_b dz2[b][k] * a1[b][j]
+    for (int idx = tid; idx < N2 * kB1Feat; idx += kB1Threads) {
+        const int k = idx / kB1Feat, ff = idx % kB1Feat;
+        float s = 0.f;
+        for (int b = 0; b < B; ++b) s += sdz2[b * ldz + k] * sa1[b * kB1Feat + ff];
+        put(a.dW2 + (size_t)k * N1 + j0 + ff, s, acc_mode);
     }
 }
 
 // ------------------------------------------------------------------ backward, launch 2: dW1 and dx
-constexpr int kB1Threads = 256;
-constexpr int kJTile = 8;        // features per dW1 block
-constexpr int kKTile = 64;       // input columns per dx block
-__global__ void __launch_bounds__(kB1Threads) head_bwd_l1_kernel(const HeadBwdArgs a, int n_jblocks) {
+// blocks [0, n_j)      : dW1 rows for 8 features, thread = input column (coalesced)
+// blocks [n_j, +n_k*8) : dx for 128 input columns x one eighth of the features, thread = (8 columns, batch lane);
+//                        partial sums are added to dx (zeroed by launch 1)
+constexpr int kB2Threads = 256;
+constexpr int kJTile = 8;
+constexpr int kKTile = 128;
+constexpr int kJSplit = 8;
+__global__ void __launch_bounds__(kB2Threads) head_b2_kernel(const HeadBwdArgs a, int n_jblocks) {
     extern __shared__ float sm[];
     const int B = a.B, N0 = a.N0, N1 = a.N1, tid = threadIdx.x;
     if ((int)blockIdx.x < n_jblocks) {
-        // dW1[j][k] (+)= sum_b dz1[b][j] * a0[b][k] for 8 features, all k (coalesced rows)
         float* a0s = sm;                        // [B][N0]
         float* dzt = a0s + B * N0;              // [kJTile][B]
         const int j0 = blockIdx.x * kJTile;
@@ -324,80 +306,87 @@ __global__ void __launch_bounds__(kB1Threads) head_bwd_l1_kernel(const HeadBwdAr
             const int n4 = B * N0 / 4;
             const float4* src = reinterpret_cast<const float4*>(a.a0);
 #pragma unroll 4
-            for (int i = tid; i < n4; i += kB1Threads) reinterpret_cast<float4*>(a0s)[i] = src[i];
+            for (int i = tid; i < n4; i += kB2Threads) reinterpret_cast<float4*>(a0s)[i] = src[i];
         }
-        for (int i = tid; i < kJTile * B; i += kB1Threads) {
+        for (int i = tid; i < kJTile * B; i += kB2Threads) {
             const int jj = i / B, b = i % B;
             dzt[i] = (j0 + jj < N1) ? a.dz1[b * N1 + j0 + jj] : 0.f;
         }
         __syncthreads();
-        for (int k = tid; k < N0; k += kB1Threads) {
+        for (int k = tid; k < N0; k += kB2Threads) {
             float s[kJTile];
 #pragma unroll
             for (int jj = 0; jj < kJTile; ++jj) s[jj] = 0.f;
+#pragma unroll 2
             for (int b = 0; b < B; ++b) {
                 const float xv = a0s[b * N0 + k];
 #pragma unroll
                 for (int jj = 0; jj < kJTile; ++jj) s[jj] += dzt[jj * B + b] * xv;
             }
-            float old[kJTile];
 #pragma unroll
             for (int jj = 0; jj < kJTile; ++jj)
-                old[jj] = (a.accumulate && j0 + jj < N1) ? a.dW1[(size_t)(j0 + jj) * N0 + k] : 0.f;
-#pragma unroll
-            for (int jj = 0; jj < kJTile; ++jj)
-                if (j0 + jj < N1) a.dW1[(size_t)(j0 + jj) * N0 + k] = old[jj] + s[jj];
+                if (j0 + jj < N1) put(a.dW1 + (size_t)(j0 + jj) * N0 + k, s[jj], a.accumulate);
         }
     } else {
-        // dx[b][k] = drop * sum_j dz1[b][j] * W1[j][k] for 64 columns; 4 thread groups split j
-        float* dzs = sm;                        // [N1][B]  (feature-major: one float4 run per feature)
-        float* red = dzs + N1 * B;              // [4][kKTile][B]
-        const int k0 = (blockIdx.x - n_jblocks) * kKTile;
+        const int blk = blockIdx.x - n_jblocks;
+        const int k0 = (blk / kJSplit) * kKTile, jpart = blk % kJSplit;
+        const int jper = (N1 + kJSplit - 1) / kJSplit;
+        const int jb = jpart * jper, je = min(N1, jb + jper);
+        float* dzs = sm;                        // [B][jper + 1]
+        const int ldj = jper + 1;
+        for (int i = tid; i < B * (je - jb); i += kB2Threads) {
+            const int b = i / (je - jb), jj = i % (je - jb);
+            dzs[b * ldj + jj] = a.dz1[b * N1 + jb + jj];
+        }
+        __syncthreads();
+        const int kg = tid >> 4, l = tid & 15;
+        const int k = k0 + kg * 8;
+        if (k < N0) {
+#pragma unroll 1
+            for (int c = 0; c * 16 < B; ++c) {
+                const int b = c * 16 + l;
+                const float* dz = dzs + (b < B ? b : 0) * ldj;
+                float acc[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[i] = 0.f;
 #pragma unroll 4
-        for (int i = tid; i < N1 * B; i += kB1Threads) {
-            const int b = i / N1, j = i % N1;   // coalesced read of dz1[b][j]
-            dzs[j * B + b] = a.dz1[i];
-        }
-        __syncthreads();
-        const int kk = tid % kKTile, jp = tid / kKTile;
-        const int k = k0 + kk;
-        const int jper = (N1 + 3) / 4;
-        for (int b0 = 0; b0 < B; b0 += BT) {
-            float acc[BT];
-#pragma unroll
-            for (int b = 0; b < BT; ++b) acc[b] = 0.f;
-            if (k < N0) {
-                const int jend = min(N1, (jp + 1) * jper);
-                for (int j = jp * jper; j < jend; j += 8) {
-                    float w8[8];
-#pragma unroll
-                    for (int jj = 0; jj < 8; ++jj)           // 8 weight loads in flight per trip
-                        w8[jj] = (j + jj < jend) ? __bfloat162float(a.W1[(size_t)(j + jj) * N0 + k]) : 0.f;
-#pragma unroll
-                    for (int jj = 0; jj < 8; ++jj)
-                        if (j + jj < jend) {
-#pragma unroll
-                            for (int b = 0; b < BT; ++b)
-                                if (b0 + b < B) acc[b] += dzs[(j + jj) * B + b0 + b] * w8[jj];
-                        }
+                for (int j = jb; j < je; ++j) {
+                    const uint4 w = *reinterpret_cast<const uint4*>(a.W1 + (size_t)j * N0 + k);
+                    const float d = dz[j - jb];
+                    acc[0] += d * __uint_as_float(w.x << 16); acc[1] += d * __uint_as_float(w.x & 0xFFFF0000u);
+                    acc[2] += d * __uint_as_float(w.y << 16); acc[3] += d * __uint_as_float(w.y & 0xFFFF0000u);
+                    acc[4] += d * __uint_as_float(w.z << 16); acc[5] += d * __uint_as_float(w.z & 0xFFFF0000u);
+                    acc[6] += d * __uint_as_float(w.w << 16); acc[7] += d * __uint_as_float(w.w & 0xFFFF0000u);
                 }
-            }
+                if (b < B) {
 #pragma unroll
-            for (int b = 0; b < BT; ++b)
-                if (b0 + b < B) red[(jp * kKTile + kk) * B + b0 + b] = acc[b];
-        }
-        __syncthreads();
-        for (int i = tid; i < kKTile * B; i += kB1Threads) {
-            const int b = i / kKTile, c = i % kKTile;
-            if (k0 + c < N0) {
-                float s = 0.f;
-#pragma unroll
-                for (int p = 0; p < 4; ++p) s += red[(p * kKTile + c) * B + b];
-                const size_t o = (size_t)b * N0 + k0 + c;
-                a.dx[o] = s * (a.drop ? a.drop[o] : 1.f);
+                    for (int i = 0; i < 8; ++i) {
+                        const size_t o = (size_t)b * N0 + k + i;
+                        atomicAdd(a.dx + o, acc[i] * (a.drop ? a.drop[o] : 1.f));
+                    }
+                }
             }
         }
     }
+}
+
+int launch_head_backward(const HeadBwdArgs& a, cudaStream_t st) {
+    {
+        const size_t smem = ((size_t)a.B * (a.N3 + a.N2 + 1 + kB1Feat)) * sizeof(float);
+        head_b1_kernel<<<a.N1 / kB1Feat, kB1Threads, smem, st>>>(a);
+        DNB_LAUNCH_CHECK();
+    }
+    {
+        const int n_j = dnb_ceil_div(a.N1, kJTile), n_k = dnb_ceil_div(a.N0, kKTile);
+        const size_t smem_j = ((size_t)a.B * a.N0 + kJTile * a.B) * sizeof(float);
+        const size_t smem_k = (size_t)a.B * ((a.N1 + kJSplit - 1) / kJSplit + 1) * sizeof(float);
+        const size_t smem = smem_j > smem_k ? smem_j : smem_k;
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_b2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        head_b2_kernel<<<n_j + n_k * kJSplit, kB2Threads, smem, st>>>(a, n_j);
+        DNB_LAUNCH_CHECK();
+    }
+    dnb_count_launch(2);
+    return 0;
 }
 
 }  // namespace
@@ -406,7 +395,7 @@ DNB_EXPORT int dnb_head_forward(const DnbHeadFwdDesc* d, void* stream_) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(d != nullptr, "dnb_head_forward: null descriptor");
     DNB_REQUIRE(d->B >= 1 && d->B <= kMaxB, "head: batch must be in [1,%d] (got %d)", kMaxB, d->B);
-    DNB_REQUIRE(d->N0 % 8 == 0 && d->N1 % 8 == 0, "head: N0 and N1 must be multiples of 8");
+    DNB_REQUIRE(d->N0 % 8 == 0 && d->N1 % 16 == 0, "head: N0 must be a multiple of 8 and N1 of 16");
     DNB_REQUIRE(!d->training || d->B > 1, "head: BatchNorm in training mode needs more than one sample");
     HeadFwdArgs a;
     a.x = d->x; a.drop = d->drop;
@@ -418,16 +407,15 @@ DNB_EXPORT int dnb_head_forward(const DnbHeadFwdDesc* d, void* stream_) {
     DNB_REQUIRE(a.x && a.W1 && a.W2 && a.W3 && a.xhat && a.invstd && a.a1 && a.a2 && a.logits, "head fwd: null buffer");
     DNB_REQUIRE(a.training || (a.run_mean && a.run_var), "head fwd: eval mode needs running statistics");
     {
-        const size_t smem = ((size_t)d->B * d->N0 + kL1Warps * FPW * kMaxB) * sizeof(float);
-        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_l1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        const int blocks = dnb_ceil_div(d->N1, kL1Warps * FPW);
-        head_l1_kernel<<<blocks, kL1Warps * 32, smem, st>>>(a);
+        const size_t smem = (size_t)d->B * (d->N0 + 4) * sizeof(float);
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_f1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        head_f1_kernel<<<d->N1 / kF1Feat, kF1Threads, smem, st>>>(a);
         DNB_LAUNCH_CHECK();
     }
     {
-        const size_t smem = ((size_t)d->B * (d->N1 + d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
-        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_l23_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_l23_kernel<<<1, kL23Threads, smem, st>>>(a);
+        const size_t smem = (size_t)d->B * (d->N1 + 4 + kF2Feat) * sizeof(float);
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_f2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        head_f2_kernel<<<dnb_ceil_div(d->N2, kF2Feat), kF2Threads, smem, st>>>(a);
         DNB_LAUNCH_CHECK();
     }
     dnb_count_launch(2);
@@ -438,6 +426,7 @@ DNB_EXPORT int dnb_head_backward(const DnbHeadBwdDesc* d, void* stream_) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(d != nullptr, "dnb_head_backward: null descriptor");
     DNB_REQUIRE(d->B >= 1 && d->B <= kMaxB, "head: batch must be in [1,%d] (got %d)", kMaxB, d->B);
+    DNB_REQUIRE(d->N0 % 8 == 0 && d->N1 % 16 == 0, "head: N0 must be a multiple of 8 and N1 of 16");
     HeadBwdArgs a;
     a.dlogits = d->dlogits; a.a0 = d->a0; a.drop = d->drop; a.xhat = d->xhat; a.invstd = d->invstd; a.a1 = d->a1; a.a2 = d->a2;
     a.W1 = (const __nv_bfloat16*)d->W1; a.W2 = (const __nv_bfloat16*)d->W2; a.W3 = (const __nv_bfloat16*)d->W3;
@@ -449,24 +438,7 @@ DNB_EXPORT int dnb_head_backward(const DnbHeadBwdDesc* d, void* stream_) {
     DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&
                     a.dW2 && a.db2 && a.dW3 && a.db3 && a.dx && a.dz1,
                 "head bwd: null buffer");
-    {
-        const size_t smem = ((size_t)d->B * (d->N3 + 2 * d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
-        if (d->B <= 16) head_bwd_l23_kernel<16><<<1, kB23Threads, smem, st>>>(a);
-        else if (d->B <= 32) head_bwd_l23_kernel<32><<<1, kB23Threads, smem, st>>>(a);
-        else head_bwd_l23_kernel<64><<<1, kB23Threads, smem, st>>>(a);
-        DNB_LAUNCH_CHECK();
-    }
-    {
-        const int n_j = dnb_ceil_div(d->N1, kJTile), n_k = dnb_ceil_div(d->N0, kKTile);
-        const size_t smem_j = ((size_t)d->B * d->N0 + kJTile * d->B) * sizeof(float);
-        const size_t smem_k = ((size_t)d->N1 * d->B + 4 * kKTile * d->B) * sizeof(float);
-        const size_t smem = smem_j > smem_k ? smem_j : smem_k;
-        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_bwd_l1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_bwd_l1_kernel<<<n_j + n_k, kB1Threads, smem, st>>>(a, n_j);
-        DNB_LAUNCH_CHECK();
-    }
-    dnb_count_launch(2);
-    return 0;
+    return launch_head_backward(a, st);
 }
 
 // ------------------------------------------------------------------ allocation-free backward
@@ -533,6 +505,7 @@ DNB_EXPORT int dnb_head_backward_noalloc(const DnbHeadBwdDesc* d, void* stream_)
     DNB_REQUIRE(d->N1 >= 1 && d->N1 <= kStaticMaxN1,
                 "dnb_head_backward_noalloc: N1 = %d exceeds the built-in scratch (max %d features); "
                 "use dnb_head_backward with caller-provided dz1", d->N1, kStaticMaxN1);
+    DNB_REQUIRE(d->N0 % 8 == 0 && d->N1 % 16 == 0, "dnb_head_backward_noalloc: N0 must be a multiple of 8 and N1 of 16");
     float* scratch = nullptr;
     if (int rc = static_scratch_for_current_device(&scratch)) return rc;
 
@@ -548,22 +521,5 @@ DNB_EXPORT int dnb_head_backward_noalloc(const DnbHeadBwdDesc* d, void* stream_)
     DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&
                     a.dW2 && a.db2 && a.dW3 && a.db3 && a.dx,
                 "dnb_head_backward_noalloc: null buffer");
-    {
-        const size_t smem = ((size_t)d->B * (d->N3 + 2 * d->N2) + (size_t)d->N3 * d->N2) * sizeof(float);
-        if (d->B <= 16) head_bwd_l23_kernel<16><<<1, kB23Threads, smem, st>>>(a);
-        else if (d->B <= 32) head_bwd_l23_kernel<32><<<1, kB23Threads, smem, st>>>(a);
-        else head_bwd_l23_kernel<64><<<1, kB23Threads, smem, st>>>(a);
-        DNB_LAUNCH_CHECK();
-    }
-    {
-        const int n_j = dnb_ceil_div(d->N1, kJTile), n_k = dnb_ceil_div(d->N0, kKTile);
-        const size_t smem_j = ((size_t)d->B * d->N0 + kJTile * d->B) * sizeof(float);
-        const size_t smem_k = ((size_t)d->N1 * d->B + 4 * kKTile * d->B) * sizeof(float);
-        const size_t smem = smem_j > smem_k ? smem_j : smem_k;
-        DNB_CUDA_CHECK(cudaFuncSetAttribute(head_bwd_l1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_bwd_l1_kernel<<<n_j + n_k, kB1Threads, smem, st>>>(a, n_j);
-        DNB_LAUNCH_CHECK();
-    }
-    dnb_count_launch(2);
-    return 0;
+    return launch_head_backward(a, st);
 }

@@ -140,5 +140,7 @@ def test_fused_capture_pairs_reproduce_the_weight_gradients():
         s = max(ref.abs().max().item(), 1e-6)
         assert torch.allclose(G, ref, atol=0.05 * s), (key, (G - ref).abs().max().item(), s)
         bref = mods_a[key].bias.grad
-        sb = max(bref.abs().max().item(), 1e-6)
+        # a bias in front of BatchNorm has an exactly-zero gradient: what is left is fp32 cancellation
+        # noise, so the scale is the magnitude of the summed terms, not of the (vanishing) result
+        sb = max(bref.abs().max().item(), 1e-3 * D.float().abs().sum(0).max().item(), 1e-6)
         assert torch.allclose(D.float().sum(0), bref, atol=0.05 * sb), (key, "bias")
