@@ -1,0 +1,58 @@
+"""Synthetic datasets (``data/synthetic.py``) in the reference's on-disk layout, run through OUR
+computation app (``computation/``) with the in-repo simulator — no dependency on the mounted
+reference tree (counterpart of SURVEY R15/R16 + §4.3)."""
+import json
+import os
+
+import numpy as np
+
+from dinunet_implementations_b200.data import synthetic
+from dinunet_implementations_b200.simulator import Simulator
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+COMP = os.path.join(ROOT, "computation")
+
+
+def test_fs_layout_matches_the_reference_toy_dataset(tmp_path):
+    root = str(tmp_path / "fs")
+    spec = synthetic.make_fs_dataset(root, seed=3)
+    assert [len(os.listdir(os.path.join(root, "input", f"local{i}", "simulatorRun"))) - 1 for i in range(5)] == \
+        list(synthetic.FS_SITE_SIZES)
+    sub = os.path.join(root, "input/local0/simulatorRun/subject0_aseg_stats.txt")
+    lines = open(sub).read().splitlines()
+    assert lines[0] == "Measure:volume\tsubject0" and len(lines) == 1 + 66
+    assert all(len(l.split("\t")) == 2 for l in lines[1:])
+    raw = json.load(open(os.path.join(root, "inputspec.json")))
+    assert len(raw) == 5 and raw[0]["labels_file"] == {"value": "site1_Covariate.csv"}
+    assert spec[0]["input_size"] == 66 and spec[0]["hidden_sizes"] == [256, 128, 64, 32]
+    from dinunet_implementations_b200.tasks.fs import parse_aseg_stats
+    x = parse_aseg_stats(sub)
+    assert x.shape == (66,) and abs(x.max() - 1.0) < 1e-12
+
+
+def test_fs_three_sites_train_to_success_and_learn(tmp_path):
+    root = str(tmp_path / "fs")
+    synthetic.make_fs_dataset(root, site_sizes=(60, 40, 50), seed=1, effect=0.6)
+    sim = Simulator.from_data_path(COMP, root, str(tmp_path / "work"), num_sites=3,
+                                   overrides={"epochs": 6, "num_reducers": 0, "patience": 50, "num_workers": 0})
+    out = sim.run(max_rounds=5000)
+    assert out["phase"] == "success"
+    log = json.load(open(os.path.join(str(tmp_path / "work"), "output/remote/simulatorRun/FS-Classification/fold_0/logs.json")))
+    loss, auc = log["test_metrics"][0]
+    assert np.isfinite(loss) and auc > 0.7, log["test_metrics"]      # planted signal is learnable
+
+
+def test_ica_two_sites_cpu(tmp_path):
+    root = str(tmp_path / "ica")
+    spec = synthetic.make_ica_dataset(root, num_sites=2, subjects_per_site=12, num_components=6, temporal_size=40,
+                                      window_size=5, window_stride=5, input_size=8, hidden_size=12, gpus_per_site=False)
+    assert spec[1]["labels_file"] == "S2_2.csv"
+    arr = np.load(os.path.join(root, "input/local0/simulatorRun", spec[0]["data_file"]))
+    assert arr[arr.files[0]].shape == (12, 6, 40)
+    sim = Simulator.from_data_path(COMP, root, str(tmp_path / "work"), num_sites=2,
+                                   overrides={"task_id": "ICA-Classification", "epochs": 1, "num_reducers": 0,
+                                              "batch_size": 4, "num_workers": 0, "split_ratio": [0.5, 0.25, 0.25]})
+    out = sim.run(max_rounds=2000)
+    assert out["phase"] == "success"
+    assert os.path.exists(os.path.join(str(tmp_path / "work"),
+                                       "output/remote/simulatorRun/ICA-Classification/fold_0/logs.json"))
