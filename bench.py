@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "recon-nccl"])
     ap.add_argument("--batch", type=int, default=16, help="per-site batch (reference local.py:33)")
     ap.add_argument("--precision-bits", default="16", choices=["16", "32"], help="gradient wire format")
+    ap.add_argument("--hidden", type=int, default=384,
+                    help="LSTM hidden size (384 = BASELINE config; 348 = the reference's datasets/icalstm/inputspec.json)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--eager", action="store_true", help="ours: eager model + fused aggregation only")
     ap.add_argument("--no-graph", action="store_true", help="ours: fused kernels launched one by one (profiling)")
@@ -167,7 +169,7 @@ def build_recon_nccl(args, world, device):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     torch.manual_seed(1)
-    net = mod.ICALstm(input_size=256, hidden_size=384, num_comps=C, window_size=W, num_cls=2).to(device)
+    net = mod.ICALstm(input_size=256, hidden_size=args.hidden, num_comps=C, window_size=W, num_cls=2).to(device)
     opt = torch.optim.Adam(net.parameters(), lr=1e-3)
     params = [q for q in net.parameters()]
 
@@ -216,7 +218,7 @@ def main():
     engine = None
     if args.impl == "ours":
         tr = make_ica_trainer(local_rank, batch_size=args.batch, precision_bits=args.precision_bits,
-                              fused=not args.eager)
+                              fused=not args.eager, hidden_size=args.hidden)
         engine = DeviceEngine(tr, use_graph=not (args.eager or args.no_graph))
 
         def step(batch):
@@ -276,7 +278,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if not args.eager and args.impl == "ours" else "fp32",
             "data": "synthetic", "gpu_launches": int(round(launches * timed_launch_frac)) if args.impl == "ours" else 0,
             "clocks": clocks, "e2e": e2e,
-            "config": {"model": "ICALstm(input 256, hidden 384, comps 100, window 10, S 98, cls 2)",
+            "config": {"model": "ICALstm(input 256, hidden %d, comps 100, window 10, S 98, cls 2)" % args.hidden,
                        "global_batch": world * args.batch, "seq_len": S, "parallelism": f"dp{world} (1 site per GPU)",
                        "agg_engine": "dSGD", "precision_bits": args.precision_bits, "optimizer": "adam",
                        "l2": "inputs rotate through a pool of %d MB > 126 MB L2" % (len(dev_pool) * bytes_in >> 20)},

@@ -34,9 +34,86 @@ def supported(model, x):
     H, D = lstm.hidden_size, lstm.num_direction
     cls = model.classifier
     feat = model.num_comp * model.window_size
-    return (x.dim() == 4 and x.shape[0] <= 64 and lstm_supported(H, D) and model.input_size % 8 == 0
-            and feat % 8 == 0 and cls[1].in_features % 8 == 0 and cls[4].in_features % 2 == 0
-            and (not model.training or x.shape[0] > 1))
+    # H that is not a multiple of 32 (the reference inputspec's hidden_size 348 -> 174 per direction)
+    # runs zero-padded to the next multiple (``_Padded``), so only the padded size has to fit
+    return (x.dim() == 4 and x.shape[0] <= 64 and lstm_supported(_ceil32(H), D) and model.input_size % 8 == 0
+            and feat % 8 == 0 and cls[1].in_features == H * D and cls[1].out_features % 16 == 0
+            and cls[4].in_features % 2 == 0 and (not model.training or x.shape[0] > 1))
+
+
+def _ceil32(h):
+    return (int(h) + 31) // 32 * 32
+
+
+class _Padded:
+    """Zero-padded operands for a per-direction hidden size ``H`` that is not a multiple of 32.
+
+    The recurrence kernels tile the hidden units in blocks of 32 (one CTA of the cluster each), so
+    ``H = 174`` runs as ``Hp = 192``.  Padding is exact, not approximate: a padded unit has zero
+    weights and biases, so its pre-activations are 0, ``g = tanh(0) = 0`` keeps its cell at 0 and
+    ``h = o * tanh(0) = 0``; nothing reads it (zero columns in ``W_hh`` and in the first classifier
+    layer), so its gradient is 0 too.  Buffers are persistent (allocated once per model and device,
+    the pad region is written only at allocation), which keeps the step CUDA-graph capturable:
+    per step there are 9 strided copies in (bf16 shadows -> padded operands), one memset of the
+    padded gradient staging area and 9 strided adds out (staging -> ``param.grad``).
+    """
+
+    def __init__(self, model, dev):
+        cells = list(model.lstm.lstms)
+        self.D, self.H, self.E = len(cells), model.lstm.hidden_size, model.input_size
+        self.Hp = _ceil32(self.H)
+        self.N1 = model.classifier[1].out_features
+        D, Hp, E, N1 = self.D, self.Hp, self.E, self.N1
+        z16 = lambda *sh: torch.zeros(*sh, device=dev, dtype=torch.bfloat16)
+        self.w_ih, self.whh, self.W1 = z16(D * 4 * Hp, E), z16(D, 4 * Hp, Hp), z16(N1, D * Hp)
+        self.b_ih = torch.zeros(D * 4 * Hp, device=dev)
+        self.b_hh = torch.zeros(D, 4 * Hp, device=dev)
+        sizes = dict(g_w_ih=D * 4 * Hp * E, g_whh=D * 4 * Hp * Hp, g_W1=N1 * D * Hp, g_b_ih=D * 4 * Hp, g_b_hh=D * 4 * Hp)
+        self.stage = torch.zeros(sum(sizes.values()), device=dev)
+        off = 0
+        for k, n in sizes.items():
+            setattr(self, k, self.stage[off:off + n])
+            off += n
+        self.g_w_ih = self.g_w_ih.view(D * 4 * Hp, E)
+        self.g_whh = self.g_whh.view(D, 4 * Hp, Hp)
+        self.g_W1 = self.g_W1.view(N1, D * Hp)
+        self.g_b_ih = self.g_b_ih.view(D, 4 * Hp)
+        self.g_b_hh = self.g_b_hh.view(D, 4 * Hp)
+
+    @staticmethod
+    def of(model, dev):
+        st = model.__dict__.setdefault("_pad_state", {})
+        key = (dev.type, dev.index)
+        if key not in st:
+            st[key] = _Padded(model, dev)
+        return st[key]
+
+    def fill(self, model):
+        D, H, Hp, E, N1 = self.D, self.H, self.Hp, self.E, self.N1
+        for d, c in enumerate(model.lstm.lstms):
+            self.w_ih.view(D, 4, Hp, E)[d, :, :H].copy_(_w16(model, c.i2h.weight).view(4, H, E))
+            self.whh.view(D, 4, Hp, Hp)[d, :, :H, :H].copy_(_w16(model, c.h2h.weight).view(4, H, H))
+            self.b_ih.view(D, 4, Hp)[d, :, :H].copy_(c.i2h.bias.detach().view(4, H))
+            self.b_hh.view(D, 4, Hp)[d, :, :H].copy_(c.h2h.bias.detach().view(4, H))
+        self.W1.view(N1, D, Hp)[:, :, :H].copy_(_w16(model, model.classifier[1].weight).view(N1, D, H))
+
+    def unpad(self, t):
+        """``[rows, D*Hp] -> [rows, D*H]`` (copy)."""
+        return t.reshape(t.shape[0], self.D, self.Hp)[:, :, :self.H].reshape(t.shape[0], self.D * self.H)
+
+    def gates(self, t, d):
+        """Direction ``d`` of a ``[rows, D*4*Hp]`` gate tensor without the pad units -> ``[rows, 4H]``."""
+        return t.reshape(t.shape[0], self.D, 4, self.Hp)[:, d, :, :self.H].reshape(t.shape[0], 4 * self.H)
+
+    def scatter_grads(self, model):
+        """Add the staged (padded) gradients into the real ``param.grad`` tensors."""
+        D, H, Hp, E, N1 = self.D, self.H, self.Hp, self.E, self.N1
+        for d, c in enumerate(model.lstm.lstms):
+            _grad_buf(c.i2h.weight).view(4, H, E).add_(self.g_w_ih.view(D, 4, Hp, E)[d, :, :H])
+            _grad_buf(c.h2h.weight).view(4, H, H).add_(self.g_whh.view(D, 4, Hp, Hp)[d, :, :H, :H])
+            _grad_buf(c.i2h.bias).view(4, H).add_(self.g_b_ih.view(D, 4, Hp)[d, :, :H])
+            _grad_buf(c.h2h.bias).view(4, H).add_(self.g_b_hh.view(D, 4, Hp)[d, :, :H])
+        _grad_buf(model.classifier[1].weight).view(N1, D, H).add_(self.g_W1.view(N1, D, Hp)[:, :, :H])
 
 
 def _w16(model, p):
@@ -94,9 +171,16 @@ class _ICALstmFn(torch.autograd.Function):
         enc = gemm_bf16(xb, _w16(model, enc_l.weight), out_dtype=torch.bfloat16, bias_n=enc_l.bias.detach(),
                         relu=True, out_t=encT)
         # 3. input projection for every timestep, both directions
-        w_ih = [_w16(model, c.i2h.weight) for c in cells]
+        pad = None
+        if H % 32:
+            pad = _Padded.of(model, x.device)
+            pad.fill(model)
+            H = pad.Hp
+        w_ih = [_w16(model, c.i2h.weight) for c in cells] if pad is None else [pad.w_ih]
         PX = torch.empty(S * B, D * 4 * H, device=x.device, dtype=torch.float32)
-        if D == 2 and _adjacent(w_ih[0], w_ih[1]) and _adjacent(cells[0].i2h.bias.detach(), cells[1].i2h.bias.detach()):
+        if pad is not None:
+            gemm_bf16(enc, pad.w_ih, out=PX, bias_n=pad.b_ih)
+        elif D == 2 and _adjacent(w_ih[0], w_ih[1]) and _adjacent(cells[0].i2h.bias.detach(), cells[1].i2h.bias.detach()):
             w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
             b_cat = _span(cells[0].i2h.bias.detach(), (D * 4 * H,), (1,))
             gemm_bf16(enc, w_cat, out=PX, bias_n=b_cat)
@@ -104,16 +188,22 @@ class _ICALstmFn(torch.autograd.Function):
             for d in range(D):
                 gemm_bf16(enc, w_ih[d], out=PX[:, d * 4 * H:(d + 1) * 4 * H], bias_n=cells[d].i2h.bias.detach())
         # 4. recurrence
-        whh = [_w16(model, c.h2h.weight) for c in cells]
-        bhh = [c.h2h.bias.detach() for c in cells]
+        if pad is None:
+            whh = [_w16(model, c.h2h.weight) for c in cells]
+            bhh = [c.h2h.bias.detach() for c in cells]
+        else:
+            whh, bhh = [pad.whh[d] for d in range(D)], [pad.b_hh[d] for d in range(D)]
         Hmean, hT, cT, C, Hprev = lstm_forward(PX, whh, bhh, B, S, H, D)
+        if pad is not None:
+            hT, cT = pad.unpad(hT), pad.unpad(cT)
         # 5. head
-        N0 = cls[1].in_features
+        N0 = D * H
         drop = None
         p_drop = cls[0].p
         if training and p_drop > 0:
             drop = torch.empty(B, N0, device=x.device, dtype=torch.float32).bernoulli_(1 - p_drop).div_(1 - p_drop)
-        W1, W2, W3 = _w16(model, cls[1].weight), _w16(model, cls[4].weight), _w16(model, cls[6].weight)
+        W1 = _w16(model, cls[1].weight) if pad is None else pad.W1
+        W2, W3 = _w16(model, cls[4].weight), _w16(model, cls[6].weight)
         bn = cls[2]
         logits, head_saved = head_forward(Hmean, drop, W1, cls[1].bias.detach(), bn.weight.detach(), bn.bias.detach(),
                                           bn.running_mean, bn.running_var, W2, cls[4].bias.detach(), W3,
@@ -123,6 +213,7 @@ class _ICALstmFn(torch.autograd.Function):
 
         ctx.model = model
         ctx.dims = (B, S, E, H, D)
+        ctx.pad = pad
         ctx.saved = (xT, enc, encT, PX, C, Hprev, whh, w_ih, head_saved)
         ctx.mark_non_differentiable(hT, cT)
         return logits, hT, cT
@@ -141,8 +232,12 @@ class _ICALstmFn(torch.autograd.Function):
         dev = dlogits.device
 
         capture = getattr(model, "_dad_capture", False)
+        pad = ctx.pad                               # H here is the padded size when pad is set
+        if pad is not None:
+            pad.stage.zero_()
         # 6. head backward (accumulates into the parameter gradients)
-        grads = dict(dW1=_grad_buf(cls[1].weight), db1=_grad_buf(cls[1].bias), dbn_w=_grad_buf(bn.weight),
+        grads = dict(dW1=_grad_buf(cls[1].weight) if pad is None else pad.g_W1,
+                     db1=_grad_buf(cls[1].bias), dbn_w=_grad_buf(bn.weight),
                      dbn_b=_grad_buf(bn.bias), dW2=_grad_buf(cls[4].weight), db2=_grad_buf(cls[4].bias),
                      dW3=_grad_buf(cls[6].weight), db3=_grad_buf(cls[6].bias))
         dHmean = head_backward(dlogits, head_saved, grads, accumulate=True)
@@ -155,7 +250,7 @@ class _ICALstmFn(torch.autograd.Function):
             dz2 = (dl @ hs["W3"].float()) * (hs["a2"] > 0)
             pairs = {"classifier.6": (dl, hs["a2"]), "classifier.4": (dz2, hs["a1"])}
             # dz1 is what head_backward handed from its first to its second launch
-            pairs["classifier.1"] = (hs["dz1"], hs["a0"])
+            pairs["classifier.1"] = (hs["dz1"], hs["a0"] if pad is None else pad.unpad(hs["a0"]))
             model._dad_pairs = pairs
 
         # Independent pieces of the backward run on side streams (parallel branches when the step is
@@ -163,7 +258,9 @@ class _ICALstmFn(torch.autograd.Function):
         # (which occupies only 2 x H/32 SMs), and the three weight-gradient chains run side by side.
         main = torch.cuda.current_stream(dev)
         s1, s2 = _side_streams(dev)
-        if D == 2 and _adjacent(w_ih[0], w_ih[1]):
+        if pad is not None:
+            w_cat = pad.w_ih
+        elif D == 2 and _adjacent(w_ih[0], w_ih[1]):
             w_cat = _span(w_ih[0], (D * 4 * H, E), (E, 1))
         else:
             w_cat = torch.cat(w_ih, 0)
@@ -175,8 +272,11 @@ class _ICALstmFn(torch.autograd.Function):
             ev_side.record(s1)
 
         # 7. BPTT
-        db_ih = [_grad_buf(c.i2h.bias) for c in cells]
-        db_hh = [_grad_buf(c.h2h.bias) for c in cells]
+        if pad is None:
+            db_ih = [_grad_buf(c.i2h.bias) for c in cells]
+            db_hh = [_grad_buf(c.h2h.bias) for c in cells]
+        else:
+            db_ih, db_hh = [pad.g_b_ih[d] for d in range(D)], [pad.g_b_hh[d] for d in range(D)]
         dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True)
         ev_dp = torch.cuda.Event()
         ev_dp.record(main)
@@ -186,11 +286,15 @@ class _ICALstmFn(torch.autograd.Function):
             main.wait_event(ev_side)
             for dd in range(D):
                 sl = slice(dd * 4 * H, (dd + 1) * 4 * H)
-                model._dad_pairs[f"lstm.lstms.{dd}.i2h"] = (dP[:, sl], enc)
-                model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (dP[:, sl], Hprev[:, dd * H:(dd + 1) * H])
+                delta = dP[:, sl] if pad is None else pad.gates(dP, dd)
+                hp = Hprev[:, dd * H:(dd + 1) * H] if pad is None else Hprev[:, dd * H:dd * H + pad.H]
+                model._dad_pairs[f"lstm.lstms.{dd}.i2h"] = (delta, enc)
+                model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (delta, hp)
             d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
             gemm_bf16(dP, w_ihT, out=d_enc, mask=enc)
             model._dad_pairs["encoder.0"] = (d_enc, xT.t())
+            if pad is not None:
+                pad.scatter_grads(model)
             return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
         # branch A (s2): through the input projection and the encoder ReLU (bias gradient as column sums,
@@ -210,16 +314,20 @@ class _ICALstmFn(torch.autograd.Function):
         s1.wait_event(ev_dpt)
         with torch.cuda.stream(s1):
             for dd, c in enumerate(cells):
-                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H], out=_grad_buf(c.h2h.weight),
-                          accumulate=True, split_k=0)
+                gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], HprevT[dd * H:(dd + 1) * H],
+                          out=_grad_buf(c.h2h.weight) if pad is None else pad.g_whh[dd], accumulate=True, split_k=0)
         g_ih = [_grad_buf(c.i2h.weight) for c in cells]
-        if D == 2 and _adjacent(g_ih[0], g_ih[1]):
+        if pad is not None:
+            gemm_bf16(dPT, encT, out=pad.g_w_ih, accumulate=True, split_k=0)
+        elif D == 2 and _adjacent(g_ih[0], g_ih[1]):
             gemm_bf16(dPT, encT, out=_span(g_ih[0], (D * 4 * H, E), (E, 1)), accumulate=True, split_k=0)
         else:
             for dd in range(D):
                 gemm_bf16(dPT[dd * 4 * H:(dd + 1) * 4 * H], encT, out=g_ih[dd], accumulate=True, split_k=0)
         main.wait_stream(s1)
         main.wait_stream(s2)
+        if pad is not None:
+            pad.scatter_grads(model)
         return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
 
 

@@ -24,6 +24,10 @@ def _pair(kw, seed=0):
     (dict(input_size=256, hidden_size=384, num_comps=100, window_size=10, num_cls=2), 16, 98),
     (dict(input_size=64, hidden_size=128, num_comps=12, window_size=6, num_cls=3), 7, 11),
     (dict(input_size=32, hidden_size=64, num_comps=8, window_size=5, num_cls=2), 33, 5),
+    # the reference's own ICA inputspec (datasets/icalstm/inputspec.json:30): hidden 348 -> H = 174 per
+    # direction, not a multiple of the 32-unit CTA tile -> zero-padded operands (ops/icalstm_fused._Padded)
+    (dict(input_size=256, hidden_size=348, num_comps=100, window_size=10, num_cls=2), 16, 98),
+    (dict(input_size=32, hidden_size=40, num_comps=8, window_size=5, num_cls=2), 9, 7),
 ])
 @pytest.mark.parametrize("mode", ["eval", "train"])
 def test_fused_icalstm_matches_eager(kw, B, S, mode):
@@ -34,6 +38,8 @@ def test_fused_icalstm_matches_eager(kw, B, S, mode):
     x = torch.randn(B, S, kw["num_comps"], kw["window_size"], device="cuda")
     y = torch.randint(0, kw["num_cls"], (B,), device="cuda")
     lo_r, (h_r, c_r) = ref(x)
+    from dinunet_implementations_b200.ops import icalstm_fused
+    assert icalstm_fused.supported(fused, x), "config must run on the kernel path, not the eager fallback"
     lo_f, (h_f, c_f) = fused(x)
     torch.cuda.synchronize()
     assert torch.allclose(lo_f, lo_r, atol=3e-2, rtol=3e-2), (lo_f - lo_r).abs().max()
