@@ -33,12 +33,21 @@ def supported(model, x):
     lstm = model.lstm
     H, D = lstm.hidden_size, lstm.num_direction
     cls = model.classifier
-    feat = model.num_comp * model.window_size
     # H that is not a multiple of 32 (the reference inputspec's hidden_size 348 -> 174 per direction)
     # runs zero-padded to the next multiple (``_Padded``), so only the padded size has to fit
     return (x.dim() == 4 and x.shape[0] <= 64 and lstm_supported(_ceil32(H), D) and model.input_size % 8 == 0
-            and feat % 8 == 0 and cls[1].in_features == H * D and cls[1].out_features % 16 == 0
+            and cls[1].in_features == H * D and cls[1].out_features % 16 == 0
             and cls[4].in_features % 2 == 0 and (not model.training or x.shape[0] > 1))
+
+
+def _pitched_copy(model, w):
+    st = model.__dict__.setdefault("_pitched", {})
+    key = (w.device.index, tuple(w.shape))
+    if key not in st:
+        st[key] = torch.zeros(w.shape[0], (w.shape[1] + 7) // 8 * 8, device=w.device, dtype=torch.bfloat16)
+    v = st[key][:, :w.shape[1]]
+    v.copy_(w)
+    return v
 
 
 def _ceil32(h):
@@ -168,8 +177,12 @@ class _ICALstmFn(torch.autograd.Function):
         # 2. encoder: relu(x W^T + b), plus the transposed copy the i2h weight-gradient GEMM needs
         BSp = (S * B + 7) // 8 * 8
         encT = torch.empty(E, BSp, device=x.device, dtype=torch.bfloat16)[:, :S * B]
-        enc = gemm_bf16(xb, _w16(model, enc_l.weight), out_dtype=torch.bfloat16, bias_n=enc_l.bias.detach(),
-                        relu=True, out_t=encT)
+        w_enc = _w16(model, enc_l.weight)
+        if w_enc.shape[1] % 8:
+            # comps*window not a multiple of 8 (e.g. the class defaults 53 x 20): TMA needs a 16-byte row
+            # pitch, so the operand is a persistent copy with the pitch rounded up (the activations already are)
+            w_enc = _pitched_copy(model, w_enc)
+        enc = gemm_bf16(xb, w_enc, out_dtype=torch.bfloat16, bias_n=enc_l.bias.detach(), relu=True, out_t=encT)
         # 3. input projection for every timestep, both directions
         pad = None
         if H % 32:

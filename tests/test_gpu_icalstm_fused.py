@@ -28,6 +28,9 @@ def _pair(kw, seed=0):
     # direction, not a multiple of the 32-unit CTA tile -> zero-padded operands (ops/icalstm_fused._Padded)
     (dict(input_size=256, hidden_size=348, num_comps=100, window_size=10, num_cls=2), 16, 98),
     (dict(input_size=32, hidden_size=40, num_comps=8, window_size=5, num_cls=2), 9, 7),
+    # class defaults of the reference model (comps/icalstm/models.py:70-71): 53 components x window 20
+    (dict(input_size=256, hidden_size=256, num_comps=53, window_size=20, num_cls=2), 8, 12),
+    (dict(input_size=32, hidden_size=64, num_comps=7, window_size=5, num_cls=2), 5, 6),
 ])
 @pytest.mark.parametrize("mode", ["eval", "train"])
 def test_fused_icalstm_matches_eager(kw, B, S, mode):
