@@ -25,6 +25,19 @@ from ..distrib import get_engine
 from ..utils import logger, save_json
 
 
+def write_test_metrics_csv(path, fold, cols, row, met):
+    """One header line + one row per fold; columns = the ``log_header`` names, then whichever of
+    accuracy / f1 / precision / recall the metrics object also offers."""
+    cols, extra = list(cols), []
+    for nm in ("accuracy", "f1", "precision", "recall"):
+        if nm not in [c.lower() for c in cols] and hasattr(met, nm):
+            cols.append(nm)
+            extra.append(round(float(getattr(met, nm)), 5))
+    with open(path, "w") as f:
+        f.write(",".join(["fold"] + cols[:len(row) + len(extra)]) + "\n")
+        f.write(",".join([f"fold_{fold}"] + [str(v) for v in list(row) + extra]) + "\n")
+
+
 class COINNRemote:
     def __init__(self, cache=None, input=None, state=None, **kw):
         self.cache = cache if cache is not None else {}
@@ -219,16 +232,8 @@ class COINNRemote:
         d = self._log_dir()
         keep = {k: v for k, v in self.cache.items() if not str(k).startswith("_")}
         save_json(os.path.join(d, "logs.json"), keep)
-        row = tr.log_row(avg, met)
-        cols = self._header_cols()
-        extra = []
-        for nm in ("accuracy", "f1", "precision", "recall"):
-            if nm not in [c.lower() for c in cols] and hasattr(met, nm):
-                cols.append(nm)
-                extra.append(round(float(getattr(met, nm)), 5))
-        with open(os.path.join(d, "test_metrics.csv"), "w") as f:
-            f.write(",".join(["fold"] + cols[:len(row) + len(extra)]) + "\n")
-            f.write(",".join([f"fold_{self.cache['fold']}"] + [str(v) for v in row + extra]) + "\n")
+        write_test_metrics_csv(os.path.join(d, "test_metrics.csv"), self.cache["fold"], self._header_cols(),
+                               tr.log_row(avg, met), met)
         try:
             from ..utils.plotter import plot_progress
             plot_progress(self.cache, d, name="global")

@@ -130,10 +130,19 @@ class SiteGroup:
     def use_flags(self):
         return self.backend == "ipc"
 
-    def close(self):
+    def close(self, barrier=None):
+        """Unmap the peers' arenas, then free our own.  In ipc mode pass ``barrier`` (e.g.
+        ``torch.distributed.barrier``): an arena must not be freed while a peer still has it mapped
+        or a kernel of a peer may still touch it."""
         l = native.lib()
+        if self._owned or self._opened:
+            torch.cuda.synchronize(self.device)
+        if barrier is not None:
+            barrier()
         for q in self._opened:
             l.dnb_ipc_close_handle(ctypes.c_void_p(q))
+        if barrier is not None:
+            barrier()
         for p in self._owned:
             l.dnb_arena_free(ctypes.c_void_p(p))
         self._opened, self._owned = [], []

@@ -131,6 +131,13 @@ class FusedDSGD:
                 m._bf16_shadow = shadow_map
         return ps
 
+    def sync_shadow(self, site=None):
+        """Re-derive the bf16 shadow from the fp32 parameters (after a checkpoint load or any other
+        in-place write to the parameters that did not go through the kernel)."""
+        if self.shadow is not None:
+            for s in ([site] if site is not None else self.sites_here()):
+                self.shadow[s].copy_(self.params[s])
+
     def pack_grads(self, site=None):
         """16-bit wire only: cast the fp32 staging gradients into the peer-visible wire buffer."""
         if self._grad_staging:

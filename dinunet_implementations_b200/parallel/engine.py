@@ -254,6 +254,34 @@ class DeviceEngine:
         self._pending = []
         return out
 
+    # ------------------------------------------------------------------ parameter I/O
+    def sync_shadow(self):
+        """Call after writing parameters in place (``load_state_dict``, checkpoint load, broadcast):
+        the kernels read bf16 copies of the weights, which are otherwise refreshed only by the fused
+        optimiser step."""
+        if self.agg_engine == "dSGD":
+            self.fused.sync_shadow(self.site)
+        else:
+            for o in self.fused.opt:
+                o.f.sync_shadow()
+
+    def load_checkpoint(self, name="best.pt", full_path=None):
+        """Load model weights (reference checkpoint format) into the live flat buffers."""
+        out = self.trainer.load_checkpoint(name=name, full_path=full_path, load_optimizer_state=False)
+        self.sync_shadow()
+        return out
+
+    def close(self):
+        """Release the graph and the peer-mapped arenas (collective in multi-process runs)."""
+        import torch.distributed as dist
+        self._graph = self._static_in = self._static_out = None
+        torch.cuda.synchronize(self.device)
+        multi = self.group.backend == "ipc" and dist.is_available() and dist.is_initialized()
+        self.group.close(barrier=dist.barrier if multi else None)
+        for o in getattr(self.fused, "opt", []) or []:
+            if hasattr(o, "group"):
+                o.group.close()
+
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, dataset, mode="validation"):
         """Local evaluation, then merge the sufficient statistics across sites."""
