@@ -13,6 +13,7 @@ sites' gradients → unscale → Adam/SGD → push updated parameters → barrie
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -85,6 +86,12 @@ class FusedDSGD:
             self.set_lr(self.lr)
         self._descs = None
         self._grad_staging = None   # per-site fp32 grads when the wire is 16-bit
+        # Race-detection aid: with DINUNET_DEBUG_POISON=1 the peer-visible gradient buffer is
+        # filled with NaN right after every aggregation launch.  The kernel's closing barrier guarantees
+        # that all peers have finished reading it by then, and zero_grad() clears it before the next
+        # backward — so training is unaffected unless a peer reads a buffer outside its window, in which
+        # case the NaN propagates into every site's parameters and is impossible to miss.
+        self.debug_poison = os.environ.get("DINUNET_DEBUG_POISON", "0") not in ("", "0")
 
     # ------------------------------------------------------------------ module binding
     def sites_here(self):
@@ -183,11 +190,18 @@ class FusedDSGD:
             for d in self._descs:
                 d.step, d.epoch, d.lr = 1, 0, self.lr
                 native.check(lib.dnb_dsgd_fused_step(ctypes.byref(d), st), "dnb_dsgd_fused_step")
+            self._poison()
             return
         epoch = self.group.next_epoch()
         for d in self._descs:
             d.step, d.epoch, d.lr = self.t, epoch, float(self.lr if lr is None else lr)
             native.check(lib.dnb_dsgd_fused_step(ctypes.byref(d), st), "dnb_dsgd_fused_step")
+        self._poison()
+
+    def _poison(self):
+        if self.debug_poison and self.opt != 2:
+            for s in self.sites_here():
+                self.grads[s].fill_(float("nan"))
 
     def allreduce_mean(self, out: torch.Tensor):
         """Reduce-only use of the same kernel: ``out = mean over sites of grads`` (local site)."""

@@ -18,6 +18,7 @@ simulated sites on one GPU through ``SiteGroup.local`` for tests).
 """
 from __future__ import annotations
 
+import contextlib
 import os
 
 import torch
@@ -119,6 +120,10 @@ class DeviceEngine:
                     for sub in m.modules():
                         sub._bf16_shadow = shadow
         self.steps = 0
+        self.timer = None
+        if self.cache.get("profile_enabled"):
+            from ..utils.profiler import PhaseTimer
+            self.timer = PhaseTimer(self.device)
         self.train_metrics = None
         if track_metrics:
             from ..ops.metrics import DeviceMetricBuffer
@@ -141,16 +146,44 @@ class DeviceEngine:
         return {k: (v.to(self.device, non_blocking=True) if isinstance(v, torch.Tensor) else v)
                 for k, v in batch.items()}
 
+    def _ph(self, name):
+        """Phase timer context (utils/profiler.py); a no-op unless profiling, and never inside a capture."""
+        t = self.timer
+        if t is None or not t.enabled or torch.cuda.is_current_stream_capturing():
+            return contextlib.nullcontext()
+        return t.phase(name)
+
     def _step_body(self, batch):
         self.trainer.train_mode()
-        self.fused.zero_grad(site=self.site)
-        it = self.trainer.iteration(batch)
-        it["loss"].backward()
-        self.fused.step()
+        with self._ph("zero_grad"):
+            self.fused.zero_grad(site=self.site)
+        with self._ph("forward"):
+            it = self.trainer.iteration(batch)
+        with self._ph("backward"):
+            it["loss"].backward()
+        with self._ph("aggregate+update"):
+            self.fused.step()
         if self.train_metrics is not None and it.get("out") is not None and "labels" in batch:
             # K9: scores / labels / loss of this step go to device accumulators (inside the graph too)
             self.train_metrics.append(it["out"], batch["labels"], it["loss"])
         return it
+
+    def profile_steps(self, batches, warmup=3):
+        """Eager (kernel-by-kernel) steps over ``batches`` with CUDA-event phase timing; returns
+        ``{phase: {'ms_mean','ms_max','calls'}}`` with MAX over ranks.  Advances training like
+        ``train_step``; the captured graph, if any, is left untouched."""
+        from ..utils.profiler import PhaseTimer
+        keep = self.timer
+        self.timer = PhaseTimer(self.device, enabled=False)
+        for i, b in enumerate(batches):
+            if i == warmup:
+                self.timer.enabled = True
+            with self._ph("step"):
+                self._step_body(self.to_device(b))
+            self.steps += 1
+        out = self.timer.summary(reduce=True)
+        self.timer = keep
+        return out
 
     def epoch_metrics(self, reset=True):
         """``(averages, metrics)`` of the training steps since the last call — one host sync."""

@@ -77,6 +77,32 @@ def main():
         eng.group.close()
     if rank == 0:
         print("DeviceEngine multi-site: OK", flush=True)
+
+    # race-detection mode: gradient wire buffers are NaN outside their read window; a peer that reads
+    # too early or too late would spread NaN into everyone's parameters
+    os.environ["DINUNET_DEBUG_POISON"] = "1"
+    tr = make_ica_trainer(local_rank, batch_size=8, hidden_size=64, input_size=32, num_components=8, window_size=5,
+                          temporal_size=40, seed=3, precision_bits="16")
+    eng = DeviceEngine(tr, use_graph=True, graph_warmup=2)
+    assert eng.fused.debug_poison
+    gen = torch.Generator().manual_seed(2000 + rank)
+    for _ in range(40):
+        batch = {"inputs": torch.randn(8, 8, 8, 5, generator=gen), "labels": torch.randint(0, 2, (8,), generator=gen)}
+        eng.train_step(batch)
+    torch.cuda.synchronize()
+    flat = torch.cat([p.detach().flatten() for p in eng.params])
+    assert torch.isfinite(flat).all(), "a poisoned gradient buffer was read outside its window"
+    assert torch.isnan(eng.fused.grads[rank]).all()
+    for other in gather(flat):
+        assert torch.equal(other, flat)
+    prof = eng.profile_steps([{"inputs": torch.randn(8, 8, 8, 5, generator=gen),
+                               "labels": torch.randint(0, 2, (8,), generator=gen)} for _ in range(8)], warmup=3)
+    assert set(prof) >= {"forward", "backward", "aggregate+update", "step"} and prof["step"]["calls"] == 5
+    dist.barrier()
+    eng.close()
+    os.environ.pop("DINUNET_DEBUG_POISON")
+    if rank == 0:
+        print("poisoned-buffer race check + phase profile: OK", {k: round(v["ms_mean"], 3) for k, v in prof.items()}, flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

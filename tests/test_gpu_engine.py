@@ -22,7 +22,7 @@ def _batches(n):
 def test_graph_replay_matches_eager_stepping():
     bs = _batches(8)
     e1, e2 = _engine(False), _engine(True)
-    l1 = [float(e1.train_step(b)["loss"]) for b in bs]
+    l1 = [float(e1.train_step(b)["loss"].detach()) for b in bs]
     l2 = [float(e2.train_step(b)["loss"]) for b in bs]
     assert e2._graph is not None and e2.kernels_per_step and e2.kernels_per_step >= 15
     assert max(abs(a - b) for a, b in zip(l1, l2)) < 2e-3, (l1, l2)
@@ -49,7 +49,7 @@ def test_async_pipeline_returns_every_loss():
 def test_bf16_wire_trains_close_to_fp32_wire():
     bs = _batches(6)
     e1, e2 = _engine(False, precision_bits="32"), _engine(False, precision_bits="16")
-    l1 = [float(e1.train_step(b)["loss"]) for b in bs]
+    l1 = [float(e1.train_step(b)["loss"].detach()) for b in bs]
     l2 = [float(e2.train_step(b)["loss"]) for b in bs]
     assert max(abs(a - b) for a, b in zip(l1, l2)) < 3e-2
     e1.group.close(); e2.group.close()
@@ -85,3 +85,16 @@ def test_engine_tracks_train_metrics_inside_the_graph():
     avg, met = eng.epoch_metrics()
     assert len(met.labels) == 7 * 8 and 0.0 <= met.auc <= 1.0 and avg.average > 0
     eng.group.close()
+
+
+def test_profile_steps_reports_phases():
+    from dinunet_implementations_b200.parallel.engine import DeviceEngine, make_ica_trainer
+    tr = make_ica_trainer(0, batch_size=8, hidden_size=64, input_size=32, num_components=8, window_size=5, temporal_size=40)
+    eng = DeviceEngine(tr, use_graph=False)
+    bs = [{"inputs": torch.randn(8, 8, 8, 5), "labels": torch.randint(0, 2, (8,))} for _ in range(6)]
+    prof = eng.profile_steps(bs, warmup=2)
+    assert list(prof) == ["zero_grad", "forward", "backward", "aggregate+update", "step"]
+    assert prof["step"]["calls"] == 4 and eng.steps == 6
+    parts = sum(prof[k]["ms_mean"] for k in ("zero_grad", "forward", "backward", "aggregate+update"))
+    assert 0 < parts <= prof["step"]["ms_mean"] * 1.05
+    eng.close()

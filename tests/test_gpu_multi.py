@@ -19,6 +19,7 @@ def test_fused_dsgd_over_ipc_two_sites():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "raw fused dSGD over IPC: OK" in r.stdout and "DeviceEngine multi-site: OK" in r.stdout
+    assert "poisoned-buffer race check + phase profile: OK" in r.stdout
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")

@@ -40,6 +40,15 @@ def test_fs_three_sites_train_to_success_and_learn(tmp_path):
     log = json.load(open(os.path.join(str(tmp_path / "work"), "output/remote/simulatorRun/FS-Classification/fold_0/logs.json")))
     loss, auc = log["test_metrics"][0]
     assert np.isfinite(loss) and auc > 0.7, log["test_metrics"]      # planted signal is learnable
+    # the log-summary tool (counterpart of the reference's nnlogs.ipynb) reads a work dir, a node dir or the zip
+    from dinunet_implementations_b200.tools import nnlogs
+    rdir = os.path.join(str(tmp_path / "work"), "output/remote/simulatorRun")
+    z = [f for f in os.listdir(rdir) if f.endswith(".zip")][0]
+    for src in (str(tmp_path / "work"), rdir, os.path.join(rdir, z)):
+        rows = nnlogs.summarise(src)
+        assert len(rows) == 1 and rows[0]["agg_engine"] == "dSGD" and rows[0]["fold"] == "fold_0"
+        assert abs(rows[0]["test_score"] - auc) < 1e-9 and rows[0]["total_s"] > 0 and "accuracy" in rows[0]
+    assert "dSGD [1 fold(s)]" in nnlogs.render(rows)
 
 
 def test_ica_two_sites_cpu(tmp_path):
