@@ -204,6 +204,26 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, u
         ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// D[tmem] (+)= A[tmem] * B[smem]^T.  A lives in tensor memory: lane = row, each 32-bit column holds two
+// consecutive bf16 k-elements, so one K=16 instruction reads 8 columns starting at `tmem_a`.  With a
+// narrow N the smem-operand form is bound by re-reading the 128 x 16 A tile (4 KB) from shared memory
+// on every instruction; the TMEM form reads it over the tensor-memory datapath instead.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// registers -> TMEM: this warp's 32 lanes x 8 consecutive 32-bit columns (one row per thread)
+__device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // Make an mbarrier track completion of all previously issued tcgen05.mma of this thread.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -300,6 +320,19 @@ __device__ __forceinline__ float tanh_fast(float x) {
     return y;
 }
 __device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+
+// sigmoid(s) for s in [0, 1] (the argument is itself a sigmoid: the reference cell applies the gate
+// non-linearity twice, comps/icalstm/models.py:32-37) on the FMA pipe only: 0.5 + 0.5 tanh(s/2) with the
+// odd Taylor polynomial of tanh up to y^9 (|y| <= 0.5: truncation error < 5e-6).  Keeps the MUFU unit,
+// which bounds the recurrence epilogues, for the first sigmoid and the tanh.
+__device__ __forceinline__ float sigmoid01_poly(float s) {
+    const float y = 0.5f * s, y2 = y * y;
+    float p = fmaf(y2, 62.f / 2835.f, -17.f / 315.f);
+    p = fmaf(y2, p, 2.f / 15.f);
+    p = fmaf(y2, p, -1.f / 3.f);
+    p = fmaf(y2, p, 1.f);
+    return fmaf(0.5f * y, p, 0.5f);
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -42,6 +42,8 @@ constexpr int NB = 16;           // batch tile = MMA N
 constexpr int U = 32;            // hidden units per CTA
 constexpr int kThreads = 128;
 constexpr int kMaxCtas = 8;
+constexpr int kTmemCols = 256;   // tensor memory per CTA: accumulators in columns [0, 32), the A operand from kTmemA on
+constexpr int kTmemA = 32;       // up to 128 columns = 256 k-elements per lane (fwd: H <= 256; bwd: 2 tiles x 128 gate rows)
 
 struct FwdArgs {
     float* PX;                       // [S*B, D*4H] fp32, time-major rows (row = time*B + b)
@@ -60,6 +62,7 @@ struct BwdArgs {
     const float* P;                  // [S*B, D*4H] full pre-activations saved by the forward
     const float* C;                  // [D][S][B][H]
     const __nv_bfloat16* Whh[2];
+    const __nv_bfloat16* WhhT[2];    // optional [H, 4H]
     const float* dHmean;             // [B, D*H] gradient w.r.t. the time-mean of h
     __nv_bfloat16* dP;               // [S*B, D*4H] bf16 out
     float* db_a[2];                  // bias gradients [4H] (i2h and h2h biases get the same values)
@@ -78,14 +81,31 @@ __device__ __forceinline__ uint32_t sw128_off(int rows_per_block, int row, int k
 
 __device__ __forceinline__ float dsig(float y) { return y * (1.f - y); }
 
+// Profiling aid: per-phase cycle counts of one thread (block 0, thread 0), averaged over the middle half
+// of the sequence in registers and written once at the end (dbg[i] = mean clock at stamp i relative to
+// stamp 0, so consecutive differences are mean phase lengths).
 #define DNB_STAMP(i)                                                  \
     do {                                                              \
-        if (stamp) a.dbg[(i)] = clock64();                            \
+        if (stamp) {                                                  \
+            const long long now_ = clock64();                         \
+            if ((i) > 0) stamp_acc[(i)] += now_ - stamp_last;         \
+            stamp_last = now_;                                        \
+        }                                                             \
+    } while (0)
+#define DNB_STAMP_DECL long long stamp_acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, stamp_last = 0; int stamp_n = 0
+#define DNB_STAMP_FLUSH                                               \
+    do {                                                              \
+        if (a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && stamp_n > 0) { \
+            long long cum_ = 0;                                       \
+            _Pragma("unroll") for (int i_ = 0; i_ < 12; ++i_) {                         \
+                cum_ += stamp_acc[i_];                                \
+                a.dbg[i_] = cum_ / stamp_n;                           \
+            }                                                         \
+        }                                                             \
     } while (0)
 
 // descriptor address-field increments (units of 16 bytes) of k-step `k` inside operands made of
-// 64-wide k-blocks: A blocks are 128 rows (16 KB) apart, B blocks NB rows (2 KB) apart
-__device__ __forceinline__ constexpr uint64_t koff_a(int k) { return (uint64_t)((k >> 2) * (128 * 128 / 16) + (k & 3) * 2); }
+// 64-wide k-blocks: B blocks are NB rows (2 KB) apart
 __device__ __forceinline__ constexpr uint64_t koff_b(int k) { return (uint64_t)((k >> 2) * (NB * 128 / 16) + (k & 3) * 2); }
 // forward B operand (h_{t-1}) is stored without swizzle: one K=16 step = two 128-byte core matrices
 __device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(k * (256 / 16)); }
@@ -94,16 +114,14 @@ __device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int H = a.H, KB = (H + 63) / 64;           // k-blocks of the recurrent GEMM
-    const int a_bytes = KB * 128 * 128;              // weight slice: 128 rows x (KB*64) k
+    const int H = a.H;
     // h_{t-1} as the MMA B operand: K-major, NO swizzle — 8-row x 16-byte core matrices, consecutive
     // k-chunks 128 B apart, the two 8-row groups h_sbo apart.  In this layout the 32 hidden units a CTA
     // produces are two contiguous 512-byte runs (one per row group), so a CTA hands its slice to a peer
     // with two bulk copies instead of 64 per-thread 16-byte stores.
     const int h_sbo = (H / 8) * 128;                 // bytes between the two 8-row groups
     const int h_bytes = NB * H * 2;                  // one h buffer (= 2 * h_sbo)
-    uint8_t* sA = smem;
-    uint8_t* sH = smem + a_bytes;                    // two buffers
+    uint8_t* sH = smem;                              // two buffers
     float* sAct = reinterpret_cast<float*>(sH + 2 * h_bytes);   // [4][NB][U]
     uint8_t* sStage = reinterpret_cast<uint8_t*>(sAct + 4 * NB * U);   // [2 parity][2 row groups][512 B] own h slice
     uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStage + 2 * 1024);
@@ -111,6 +129,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(hbar + 2);
 
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool mark = a.dbg != nullptr && blockIdx.x == 0 && tid == 0;
+    if (mark) a.dbg[12] = clock64();
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);     // provably warp-uniform for the compiler
     const int ncta = dnb::cluster_nctarank();
     const int cta = dnb::cluster_ctarank();
@@ -120,35 +140,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     const int nvalid = min(NB, a.B - b0);            // real batch rows in this tile
     const uint32_t h_tx_bytes = (uint32_t)(NB * H * 2);
 
-    // ---- one-time: weight slice -> swizzled smem, zero h_{-1}
-    const __nv_bfloat16* W = a.Whh[dir];
-    const int chunks_per_row = H / 8;
-    for (int base = 0; base < 128 * chunks_per_row; base += kThreads * 8) {
-        uint4 v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {                     // 8 independent 16-byte loads in flight per thread
-            const int idx = base + u * kThreads + tid;
-            if (idx < 128 * chunks_per_row) {
-                const int r = idx / chunks_per_row, ch = idx % chunks_per_row;
-                const int gr = (r >> 5) * H + cta * U + (r & 31);
-                v[u] = *reinterpret_cast<const uint4*>(W + (size_t)gr * H + ch * 8);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int idx = base + u * kThreads + tid;
-            if (idx < 128 * chunks_per_row) {
-                const int r = idx / chunks_per_row, ch = idx % chunks_per_row;
-                *reinterpret_cast<uint4*>(sA + sw128_off(128, r, ch * 8)) = v[u];
-            }
-        }
-    }
-    if (H & 63) {   // zero the unused tail of the last k-block so stale smem never feeds the MMA
-        for (int idx = tid; idx < 128 * (KB * 8 - chunks_per_row); idx += kThreads) {
-            const int r = idx / (KB * 8 - chunks_per_row), ch = chunks_per_row + idx % (KB * 8 - chunks_per_row);
-            *reinterpret_cast<uint4*>(sA + sw128_off(128, r, ch * 8)) = make_uint4(0, 0, 0, 0);
-        }
-    }
+    // ---- one-time: zero h_{-1}; the weight slice goes to tensor memory once the allocation exists
     for (int idx = tid; idx < 2 * h_bytes / 16; idx += kThreads)
         reinterpret_cast<uint4*>(sH)[idx] = make_uint4(0, 0, 0, 0);
     if (warp == 0) {
@@ -162,17 +154,42 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             if (a.S > 2) dnb::mbar_expect_tx(&hbar[0], h_tx_bytes);
         }
         __syncwarp();
-        dnb::tmem_alloc(tmem_slot, 32);
+        dnb::tmem_alloc(tmem_slot, kTmemCols);
     }
     dnb::fence_proxy_async();
     dnb::tc_fence_before();
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    dnb::cluster_sync_all();       // every CTA's buffers and barriers exist before anyone writes remotely
 
     // epilogue-1 role: thread = gate row (q = warp, u = lane)
     const int grow = warp * H + cta * U + lane;
+    // A operand = this CTA's 128 gate rows of W_hh, resident in TENSOR MEMORY for the whole sequence:
+    // lane = gate row (the same row this thread owns in the epilogue), 32-bit column j = k-elements
+    // 2j, 2j+1.  With N = 16 an smem A operand makes every K=16 instruction re-read a 4 KB tile from
+    // shared memory (>= 32 cycles at 128 B/clk — the recurrent GEMM was bound by exactly that); from
+    // TMEM the same instruction issues at the tensor pipe's own rate.
+    {
+        const uint4* wrow = reinterpret_cast<const uint4*>(a.Whh[dir] + (size_t)grow * H);
+        const uint32_t a_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + kTmemA;
+        for (int c0 = 0; c0 < H / 16; c0 += 4) {
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)                       // 8 independent 16-byte loads in flight
+                if (c0 * 2 + u < H / 8) v[u] = wrow[c0 * 2 + u];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c0 + u < H / 16) {
+                    const uint32_t r[8] = {v[2 * u].x, v[2 * u].y, v[2 * u].z, v[2 * u].w,
+                                           v[2 * u + 1].x, v[2 * u + 1].y, v[2 * u + 1].z, v[2 * u + 1].w};
+                    dnb::tmem_st_32x8(a_lane + (c0 + u) * 8, r);
+                }
+        }
+        dnb::tmem_st_wait();
+    }
+    dnb::tc_fence_before();
+    dnb::cluster_sync_all();       // every CTA's buffers and barriers exist before anyone writes remotely
+    dnb::tc_fence_after();
     const float bias = a.bhh[dir][grow];
     // epilogue-2 role: thread = (batch b2, 4 consecutive units)
     const int b2 = tid >> 3, ug = tid & 7;
@@ -194,7 +211,6 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
     // broadcast from lane 0 so the compiler keeps descriptors / TMEM address in uniform registers
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint64_t da_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sA), 0));
     const uint32_t sH_u = __shfl_sync(0xffffffffu, dnb::smem_u32(sH), 0);
     const uint64_t db_base0 = dnb::umma_desc_k_noswizzle(sH_u, 128, h_sbo);
     const uint64_t db_base1 = dnb::umma_desc_k_noswizzle(sH_u + h_bytes, 128, h_sbo);
@@ -215,31 +231,19 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     float pst[NB];
     uint2 hb_prev = make_uint2(0, 0);
 
+    DNB_STAMP_DECL;
+    if (mark) a.dbg[13] = clock64();
     for (int t = 0; t < a.S; ++t) {
-        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t == a.S / 2;
+        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
+        stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
         float px[NB];
 #pragma unroll
         for (int b = 0; b < NB; ++b) px[b] = px_next[b];
 
-        if (warp == 0) {
-            // Warp-uniform control flow + elect.sync: the descriptors stay in uniform registers and
-            // each tcgen05.mma is a single UTCHMMA (a divergent `tid == 0` branch makes ptxas wrap
-            // every MMA in a lane-election loop, ~60 cycles apiece).
-            if (t > 0) dnb::mbar_wait(&hbar[t & 1], ((t - 1) >> 1) & 1);   // h_{t-1} complete (complete_tx, as for TMA)
-            dnb::tc_fence_after();
-            const uint64_t db_base = (t & 1) ? db_base1 : db_base0;
-            if (dnb::elect_one()) {
-                if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
-#pragma unroll
-                for (int k = 0; k < 16; ++k)
-                    if (k < ksteps) dnb::umma_bf16_ss(tmem_u, da_base + koff_a(k), db_base + koff_h(k), idesc, k != 0);
-                dnb::umma_commit(mma_bar);
-            }
-            __syncwarp();
-        }
-        DNB_STAMP(1);
-        // ---- while the MMA runs: deferred stores of step t-1, prefetch of step t+1
+        // ---- first, while h_{t-1} is still in flight between the CTAs: deferred stores of step t-1 and
+        // the prefetch of step t+1 (the issuing warp does this BEFORE it waits for h, so neither the
+        // exchange latency nor the MMA ever waits for these ~35 memory instructions)
         if (t > 0) {
             float* pprev = px_ptr - px_step;
 #pragma unroll
@@ -255,14 +259,33 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
 #pragma unroll
             for (int b = 0; b < NB; ++b) px_next[b] = (b < nvalid) ? pn[(size_t)b * ldp] : 0.f;
         }
-        DNB_STAMP(2);
+        DNB_STAMP(1);
+        if (warp == 0) {
+            // Warp-uniform control flow + elect.sync: the descriptors stay in uniform registers and
+            // each tcgen05.mma is a single UTCHMMA (a divergent `tid == 0` branch makes ptxas wrap
+            // every MMA in a lane-election loop, ~60 cycles apiece).
+            if (t > 0) dnb::mbar_wait(&hbar[t & 1], ((t - 1) >> 1) & 1);   // h_{t-1} complete (complete_tx, as for TMA)
+            dnb::tc_fence_after();
+            DNB_STAMP(2);
+            const uint64_t db_base = (t & 1) ? db_base1 : db_base0;
+            if (dnb::elect_one()) {
+                if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if (k < ksteps)
+                        dnb::umma_bf16_ts(tmem_u, tmem_u + kTmemA + k * 8, db_base + koff_h(k), idesc, k != 0);
+                dnb::umma_commit(mma_bar);
+            }
+            __syncwarp();
+        }
+        DNB_STAMP(3);
         dnb::mbar_wait(mma_bar, t & 1);
         dnb::tc_fence_after();
-        DNB_STAMP(3);
+        DNB_STAMP(4);
         uint32_t acc[NB];
         dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
         dnb::tmem_ld_wait();
-        DNB_STAMP(4);
+        DNB_STAMP(5);
         // 16 independent activation chains per thread; the gate type is warp-uniform, so the branch
         // sits outside the unrolled loop and the MUFU ops of different batch columns overlap
 #pragma unroll
@@ -270,15 +293,15 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         float* act_row = sAct + warp * NB * U + lane;
         if (warp < 3) {
 #pragma unroll
-            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::sigmoid_fast(dnb::sigmoid_fast(pst[b]));
+            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::sigmoid01_poly(dnb::sigmoid_fast(pst[b]));
         } else {
 #pragma unroll
             for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::tanh_fast(pst[b]);
         }
-        DNB_STAMP(5);
+        DNB_STAMP(6);
         dnb::tc_fence_before();
         __syncthreads();
-        DNB_STAMP(6);
+        DNB_STAMP(7);
 
         // cell update: (b2, units ug*4 .. ug*4+3)
         const float4 gi = *reinterpret_cast<const float4*>(sAct + (0 * NB + b2) * U + ug * 4);
@@ -297,6 +320,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         hb.x = dnb::pack_bf16x2(hlast[0], hlast[1]);
         hb.y = dnb::pack_bf16x2(hlast[2], hlast[3]);
         hb_prev = hb;
+        DNB_STAMP(8);
         if (t + 1 < a.S) {
             // stage the slice, then (one elected thread) two 512-byte bulk copies per peer: data lands in
             // every CTA's next B operand and counts on that CTA's "h arrived" barrier (async proxy on both
@@ -305,6 +329,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             *reinterpret_cast<uint2*>(sStage + par * 1024 + stage_off) = hb;
             dnb::fence_proxy_async_smem();
             __syncthreads();
+            DNB_STAMP(9);
             if (dnb::elect_one()) {                       // one thread per warp; warp w serves peers w, w+4
                 const uint32_t src = sStage_u + par * 1024;
                 const uint32_t dst = sH_u + par * h_bytes + slice_off;
@@ -320,13 +345,14 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
                 }
             }
         }
-        DNB_STAMP(7);
+        DNB_STAMP(10);
         px_ptr += px_step;
         c_ptr += c_step;
         hp_ptr += hp_step;
-        DNB_STAMP(8);
-        DNB_STAMP(9);
+        DNB_STAMP(11);
     }
+    if (mark) a.dbg[14] = clock64();
+    DNB_STAMP_FLUSH;
     // flush the deferred stores of the last step
     {
         float* pprev = px_ptr - px_step;
@@ -347,9 +373,10 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     __syncthreads();
     if (warp == 0) {
         dnb::tc_fence_after();
-        dnb::tmem_dealloc(tmem_base, 32);
+        dnb::tmem_dealloc(tmem_base, kTmemCols);
     }
     dnb::cluster_sync_all();       // nobody leaves while a peer may still address its shared memory
+    if (mark) a.dbg[15] = clock64();
 }
 
 // ------------------------------------------------------------------------------------ backward
@@ -358,9 +385,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
     const int H = a.H;
     const int MT = (H + 127) / 128;                      // M tiles over hidden units
-    const int tile_bytes = 2 * 128 * 128;                // [128 rows][K = 128 own gate rows] = 2 k-blocks
-    uint8_t* sA = smem;                                  // MT tiles
-    uint8_t* sB = smem + MT * tile_bytes;                // dP_t slice: [NB rows][128 k] = 2 k-blocks x NB x 128 B
+    const int w_pitch = H * 2 + 16;                      // staging row pitch (+16 B: conflict-free 16-byte stores)
+    uint8_t* sW = smem;                                  // one-time staging of the weight slice [128 gate rows][H]
+    uint8_t* sB = smem + 128 * w_pitch;                  // dP_t slice: [NB rows][128 k] = 2 k-blocks x NB x 128 B
     float* sRed = reinterpret_cast<float*>(sB + 2 * NB * 128);   // [2][ncta][U][NB]
     const int ncta = dnb::cluster_nctarank();
     float* sDb = sRed + 2 * ncta * U * NB;               // [128] bias-gradient reduction
@@ -370,6 +397,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rbar + 2);
 
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool mark = a.dbg != nullptr && blockIdx.x == 0 && tid == 0;
+    if (mark) a.dbg[12] = clock64();
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int cta = dnb::cluster_ctarank();
     const int cid = blockIdx.x / ncta;
@@ -379,36 +408,30 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const uint32_t red_tx_bytes = (uint32_t)(ncta * U * NB * 4);
     const int rounds = a.S - 1;
 
-    // ---- one-time: A[unit k', own gate row j] = W_hh[j, k']  (transposed while loading)
-    for (int idx = tid; idx < MT * tile_bytes / 16; idx += kThreads)
-        reinterpret_cast<uint4*>(sA)[idx] = make_uint4(0, 0, 0, 0);
+    // ---- one-time: this CTA's 128 gate rows of W_hh -> shared memory (row-major, coalesced 16-byte
+    // loads); transposed into tensor memory below, once the allocation exists
     for (int idx = tid; idx < (2 * NB * 128) / 16; idx += kThreads)
         reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
     sDb[tid] = 0.f;
-    __syncthreads();
     const __nv_bfloat16* W = a.Whh[dir];
-    // thread = local gate row jl (consecutive lanes -> consecutive smem columns, no bank conflicts);
-    // each trip loads 4 x 8 hidden units of that row with independent 16-byte loads
-    {
-        const int jl = tid;                               // kThreads == 128 == number of local gate rows
-        const int grow = (jl >> 5) * H + cta * U + (jl & 31);
-        const __nv_bfloat16* wrow = W + (size_t)grow * H;
-        for (int c0 = 0; c0 < H / 8; c0 += 4) {
-            uint4 v[4];
+    const __nv_bfloat16* WT = a.WhhT[dir];
+    if (WT == nullptr) {
+        const int cpr = H / 8;                            // 16-byte chunks per row
+        for (int base = 0; base < 128 * cpr; base += kThreads * 8) {
+            uint4 v[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (c0 + u < H / 8) v[u] = *reinterpret_cast<const uint4*>(wrow + (c0 + u) * 8);
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (c0 + u < H / 8) {
-                    const uint32_t w32[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int kp = (c0 + u) * 8 + e;
-                        const uint16_t bits = (uint16_t)((e & 1) ? (w32[e >> 1] >> 16) : (w32[e >> 1] & 0xFFFFu));
-                        *reinterpret_cast<uint16_t*>(sA + (kp >> 7) * tile_bytes + sw128_off(128, kp & 127, jl)) = bits;
-                    }
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * kThreads + tid;
+                if (idx < 128 * cpr) {
+                    const int jl = idx / cpr, ch = idx % cpr;
+                    v[u] = *reinterpret_cast<const uint4*>(W + (size_t)((jl >> 5) * H + cta * U + (jl & 31)) * H + ch * 8);
                 }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * kThreads + tid;
+                if (idx < 128 * cpr) *reinterpret_cast<uint4*>(sW + (idx / cpr) * w_pitch + (idx % cpr) * 16) = v[u];
+            }
         }
     }
     if (warp == 0) {
@@ -421,14 +444,57 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             if (rounds > 1) dnb::mbar_expect_tx(&rbar[1], red_tx_bytes);
         }
         __syncwarp();
-        dnb::tmem_alloc(tmem_slot, 32);
+        dnb::tmem_alloc(tmem_slot, kTmemCols);
     }
     dnb::fence_proxy_async();
     dnb::tc_fence_before();
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // A operand in TENSOR MEMORY (see the forward kernel): tile mt, lane m = hidden unit mt*128 + m,
+    // 32-bit column j2 = W_hh[own gate row 2*j2, unit] | W_hh[own gate row 2*j2+1, unit] << 16 — i.e.
+    // W_hh^T restricted to this CTA's gate rows, K = 128.  Thread m reads column `unit` of the staged
+    // slice (consecutive lanes -> consecutive 2-byte elements: conflict-free).
+    for (int mt = 0; mt < MT; ++mt) {
+        const int unit = mt * 128 + tid;
+        const uint32_t a_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + kTmemA + mt * 64;
+        if (WT != nullptr) {
+            // pre-transposed weights: row `unit` of W_hh^T, the four 32-element runs of this CTA's gate rows
+            uint4 v[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+                    v[q * 4 + x] = (unit < H) ? *reinterpret_cast<const uint4*>(WT + (size_t)unit * 4 * H + q * H + cta * U + x * 8)
+                                              : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t r[8] = {v[2 * c].x, v[2 * c].y, v[2 * c].z, v[2 * c].w,
+                                       v[2 * c + 1].x, v[2 * c + 1].y, v[2 * c + 1].z, v[2 * c + 1].w};
+                dnb::tmem_st_32x8(a_lane + c * 8, r);
+            }
+            continue;
+        }
+#pragma unroll 2
+        for (int c = 0; c < 8; ++c) {
+            uint32_t r[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int j = (c * 8 + e) * 2;
+                uint32_t lo = 0, hi = 0;
+                if (unit < H) {
+                    lo = *reinterpret_cast<const uint16_t*>(sW + j * w_pitch + unit * 2);
+                    hi = *reinterpret_cast<const uint16_t*>(sW + (j + 1) * w_pitch + unit * 2);
+                }
+                r[e] = lo | (hi << 16);
+            }
+            dnb::tmem_st_32x8(a_lane + c * 8, r);
+        }
+    }
+    dnb::tmem_st_wait();
+    dnb::tc_fence_before();
     dnb::cluster_sync_all();
+    dnb::tc_fence_after();
 
     const int b2 = tid >> 3, ug = tid & 7;
     const bool b_ok = b2 < nvalid;
@@ -448,9 +514,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint64_t da_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sA), 0));
     const uint64_t db_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sB), 0));
-    const uint64_t tile_off = (uint64_t)(tile_bytes / 16);
     // where this warp's partial-dh blocks go: tile mt of warp w belongs to CTA mt*4 + w
     const uint32_t red_blk[2] = {dnb::smem_u32(sRed + (size_t)cta * U * NB),
                                  dnb::smem_u32(sRed + (size_t)ncta * U * NB + (size_t)cta * U * NB)};
@@ -480,8 +544,11 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 #pragma unroll
     for (int q = 0; q < 4; ++q) dp_store[q] = make_uint2(0, 0);
 
+    DNB_STAMP_DECL;
+    if (mark) a.dbg[13] = clock64();
     for (int t = a.S - 1; t >= 0; --t) {
-        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t == a.S / 2;
+        const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
+        stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
         float4 pq[4], cc = cc_n, cp = cp_n;
 #pragma unroll
@@ -496,7 +563,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
                     if (mt < MT) {
 #pragma unroll
                         for (int k = 0; k < 8; ++k)
-                            dnb::umma_bf16_ss(tmem_u + mt * NB, da_base + mt * tile_off + koff_a(k),
+                            dnb::umma_bf16_ts(tmem_u + mt * NB, tmem_u + kTmemA + mt * 64 + k * 8,
                                               db_base + koff_b(k), idesc, k != 0);
                     }
                 dnb::umma_commit(mma_bar);
@@ -526,7 +593,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const float si = dnb::sigmoid_fast(pi[j]), sf = dnb::sigmoid_fast(pf[j]), so = dnb::sigmoid_fast(po[j]);
-            const float i = dnb::sigmoid_fast(si), f = dnb::sigmoid_fast(sf), o = dnb::sigmoid_fast(so);
+            const float i = dnb::sigmoid01_poly(si), f = dnb::sigmoid01_poly(sf), o = dnb::sigmoid01_poly(so);
             const float g = dnb::tanh_fast(pg[j]);
             const float tc = dnb::tanh_fast(cv[j]);
             k_h[j] = o * (1.f - tc * tc);            // dh -> dc
@@ -537,6 +604,11 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             k_fg[j] = f;                             // dc_{t-1} = dct * f
         }
 
+        // pin the recompute HERE (in the shadow of the MMA and of the exchange): without a use before the
+        // waits the compiler sinks it behind them, onto the critical path
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            asm volatile("" ::"f"(k_i[j]), "f"(k_f[j]), "f"(k_g[j]), "f"(k_h[j]), "f"(k_tc[j]), "f"(k_fg[j]));
         float dh[4] = {dh_out[0], dh_out[1], dh_out[2], dh_out[3]};
         DNB_STAMP(2);
         if (t < a.S - 1) {
@@ -547,31 +619,37 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             // shared memory (16-byte chunks XOR-swizzled by unit so the owner's column reads spread over
             // banks) and shipped to the owning CTA with ONE bulk copy = one complete_tx on its barrier
             // (per-thread st.async cost one mbarrier update per 16 bytes, 768 per CTA and step).
+            uint32_t v[2][NB];
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
-                if (mt < MT) {
-                    const int dest = mt * 4 + warp;         // CTA owning units [32*dest, 32*dest+32)
-                    uint32_t v[NB];
-                    dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v);
-                    dnb::tmem_ld_wait();
-                    if (dest < ncta) {
-                        float* stg = sStg + ((((n & 1) * 4 + warp) * 2 + mt) * U * NB);
-                        const int swz = (lane >> 2) & 3;
-#pragma unroll
-                        for (int x = 0; x < 4; ++x)
-                            *reinterpret_cast<uint4*>(stg + lane * NB + ((x ^ swz) << 2)) =
-                                make_uint4(v[4 * x], v[4 * x + 1], v[4 * x + 2], v[4 * x + 3]);
-                        dnb::fence_proxy_async_smem();
-                        __syncwarp();
-                        if (dnb::elect_one())
-                            dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk[n & 1], dest), dnb::smem_u32(stg),
-                                                           U * NB * 4, dnb::mapa(rbar_local[n & 1], dest));
-                    }
-                }
+                if (mt < MT) dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v[mt]);
+            dnb::tmem_ld_wait();
             DNB_STAMP(4);
+            float* stg = sStg + (((n & 1) * 4 + warp) * 2) * U * NB;     // this warp's two blocks of round n
+            const int swz = (lane >> 2) & 3;
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+                if (mt < MT && mt * 4 + warp < ncta) {     // tile mt of warp w belongs to CTA mt*4 + w
+#pragma unroll
+                    for (int x = 0; x < 4; ++x)
+                        *reinterpret_cast<uint4*>(stg + mt * U * NB + lane * NB + ((x ^ swz) << 2)) =
+                            make_uint4(v[mt][4 * x], v[mt][4 * x + 1], v[mt][4 * x + 2], v[mt][4 * x + 3]);
+                }
+            dnb::fence_proxy_async_smem();                 // one fence for both blocks
+            __syncwarp();
+            DNB_STAMP(5);
+            if (dnb::elect_one()) {
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+                    if (mt < MT && mt * 4 + warp < ncta)
+                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk[n & 1], mt * 4 + warp),
+                                                       dnb::smem_u32(stg + mt * U * NB), U * NB * 4,
+                                                       dnb::mapa(rbar_local[n & 1], mt * 4 + warp));
+            }
+            DNB_STAMP(6);
             dnb::tc_fence_before();
             dnb::mbar_wait(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
-            DNB_STAMP(5);
+            DNB_STAMP(7);
             const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB +
                                    ((((b2 >> 2) ^ (ug & 3)) << 2) | (b2 & 3));
             float part[kMaxCtas][4];
@@ -584,7 +662,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dh[j] += part[src][j];
         }
-        DNB_STAMP(6);
+        DNB_STAMP(8);
         float dp[4][4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -606,28 +684,38 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 #pragma unroll
             for (int j = 0; j < 4; ++j) dbacc[q][j] += dp[q][j];
         }
-        DNB_STAMP(7);
+        DNB_STAMP(9);
         p_ptr += p_step;
         dp_ptr += p_step;
         c_ptr -= c_step;
         dnb::fence_proxy_async_smem();               // generic-proxy writes of sB -> visible to the MMA
-        DNB_STAMP(8);
+        DNB_STAMP(10);
         __syncthreads();
         if (tid == 0 && t < a.S - 1 && n + 2 < rounds) dnb::mbar_expect_tx(&rbar[n & 1], red_tx_bytes);   // re-arm
-        DNB_STAMP(9);
+        DNB_STAMP(11);
     }
+    if (mark) a.dbg[14] = clock64();
+    DNB_STAMP_FLUSH;
     if (b_ok) {                                      // dP of step 0
         __nv_bfloat16* dprev = dp_ptr - p_step;
 #pragma unroll
         for (int q = 0; q < 4; ++q) *reinterpret_cast<uint2*>(dprev + q * H) = dp_store[q];
     }
 
-    // bias gradients: sum over batch (threads sharing ug) — once per kernel
+    // bias gradients: sum over the batch rows — lanes that share ug inside a warp by shuffles (rows 4w..4w+3),
+    // then the four warps through shared memory (sRed is free: every incoming round has been consumed).
+    // (16-way contended shared atomics here cost ~10 us per launch.)
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) atomicAdd(&sDb[q * U + ug * 4 + j], dbacc[q][j]);
+        for (int j = 0; j < 4; ++j) {
+            float v = dbacc[q][j];
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (lane < 8) sRed[warp * 128 + q * U + ug * 4 + j] = v;
+        }
     __syncthreads();
+    sDb[tid] = sRed[tid] + sRed[128 + tid] + sRed[256 + tid] + sRed[384 + tid];
     {
         const int gr = (tid >> 5) * H + cta * U + (tid & 31);
         const float v = sDb[tid];
@@ -644,9 +732,10 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     __syncthreads();
     if (warp == 0) {
         dnb::tc_fence_after();
-        dnb::tmem_dealloc(tmem_base, 32);
+        dnb::tmem_dealloc(tmem_base, kTmemCols);
     }
     dnb::cluster_sync_all();
+    if (mark) a.dbg[15] = clock64();
 }
 
 template <typename Args>
@@ -696,8 +785,8 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
     for (int i = 0; i < d->D; ++i)
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
-    const int ncta = d->H / U, KB = (d->H + 63) / 64;
-    const size_t smem = (size_t)KB * 128 * 128 + 2 * (size_t)NB * d->H * 2 + 4 * NB * U * 4 + 2 * 1024 + 128 + 1024;
+    const int ncta = d->H / U;
+    const size_t smem = 2 * (size_t)NB * d->H * 2 + 4 * NB * U * 4 + 2 * 1024 + 128 + 1024;
     const int tiles = (d->B + NB - 1) / NB;
     return launch_cluster(lstm_fwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }
@@ -710,6 +799,7 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
     a.P = d->P; a.C = d->C; a.dHmean = d->dHmean; a.dP = reinterpret_cast<__nv_bfloat16*>(d->dP);
     for (int i = 0; i < 2; ++i) {
         a.Whh[i] = reinterpret_cast<const __nv_bfloat16*>(d->Whh[i]);
+        a.WhhT[i] = reinterpret_cast<const __nv_bfloat16*>(d->WhhT[i]);
         a.db_a[i] = d->db_ih[i];
         a.db_b[i] = d->db_hh[i];
     }
@@ -718,7 +808,7 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
     a.B = d->B; a.S = d->S; a.H = d->H; a.D = d->D;
     for (int i = 0; i < d->D; ++i) DNB_REQUIRE(a.Whh[i] && a.db_a[i], "lstm bwd: W_hh/db[%d] missing", i);
     DNB_REQUIRE(a.P && a.C && a.dHmean && a.dP, "lstm bwd: null buffer");
-    const int ncta = d->H / U, MT = (d->H + 127) / 128;
+    const int ncta = d->H / U;
     const int tiles = (d->B + NB - 1) / NB;
     if (tiles > 1 && !d->accumulate) {
         // several batch tiles add into the same bias-gradient vectors
@@ -727,6 +817,6 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
             if (a.db_b[i]) DNB_CUDA_CHECK(cudaMemsetAsync(a.db_b[i], 0, sizeof(float) * 4 * d->H, st));
         }
     }
-    const size_t smem = (size_t)MT * 2 * 128 * 128 + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + (size_t)2 * 4 * 2 * U * NB * 4 + 128 + 1024;
+    const size_t smem = (size_t)128 * (d->H * 2 + 16) + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + (size_t)2 * 4 * 2 * U * NB * 4 + 128 + 1024;
     return launch_cluster(lstm_bwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
 }

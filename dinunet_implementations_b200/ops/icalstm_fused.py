@@ -206,7 +206,20 @@ class _ICALstmFn(torch.autograd.Function):
             bhh = [c.h2h.bias.detach() for c in cells]
         else:
             whh, bhh = [pad.whh[d] for d in range(D)], [pad.b_hh[d] for d in range(D)]
+        whhT = None
+        if torch.is_grad_enabled() or any(ctx.needs_input_grad):
+            # K-major copy of W_hh for the BPTT kernel's tensor-memory operand, made on a side stream
+            # while the recurrence runs (a parallel branch when the step is a CUDA graph)
+            main = torch.cuda.current_stream(x.device)
+            s1, _ = _side_streams(x.device)
+            s1.wait_stream(main)
+            with torch.cuda.stream(s1):
+                whhT = [transpose_bf16(w) for w in whh]
+                ev_whhT = torch.cuda.Event()
+                ev_whhT.record(s1)
         Hmean, hT, cT, C, Hprev = lstm_forward(PX, whh, bhh, B, S, H, D)
+        if whhT is not None:
+            main.wait_event(ev_whhT)
         if pad is not None:
             hT, cT = pad.unpad(hT), pad.unpad(cT)
         # 5. head
@@ -228,6 +241,7 @@ class _ICALstmFn(torch.autograd.Function):
         ctx.dims = (B, S, E, H, D)
         ctx.pad = pad
         ctx.saved = (xT, enc, encT, PX, C, Hprev, whh, w_ih, head_saved)
+        ctx.whhT = whhT
         ctx.mark_non_differentiable(hT, cT)
         return logits, hT, cT
 
@@ -290,7 +304,7 @@ class _ICALstmFn(torch.autograd.Function):
             db_hh = [_grad_buf(c.h2h.bias) for c in cells]
         else:
             db_ih, db_hh = [pad.g_b_ih[d] for d in range(D)], [pad.g_b_hh[d] for d in range(D)]
-        dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True)
+        dP = lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh, accumulate=True, whhT=ctx.whhT)
         ev_dp = torch.cuda.Event()
         ev_dp.record(main)
 

@@ -36,9 +36,10 @@ def lstm_forward(px, whh, bhh, B, S, H, D, dbg=None):
     return Hmean, hT, cT, C, Hprev
 
 
-def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=False, dbg=None):
+def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=False, dbg=None, whhT=None):
     """Returns ``dP`` bf16 ``[S*B, D*4H]``; bias gradients are written into ``db_ih`` / ``db_hh``
-    (lists of D fp32 ``[4H]`` tensors)."""
+    (lists of D fp32 ``[4H]`` tensors).  ``whhT`` (optional list of D contiguous bf16 ``[H,4H]``): the
+    recurrent weights already transposed — saves the in-kernel transposition (~6 us per launch)."""
     lib = native.require_gpu()
     dP = torch.empty(S * B, D * 4 * H, device=P.device, dtype=torch.bfloat16)
     d = native.LstmBwdDesc()
@@ -46,6 +47,9 @@ def lstm_backward(P, C, whh, dHmean, B, S, H, D, db_ih, db_hh=None, accumulate=F
     assert dHmean.dtype == torch.float32 and dHmean.is_contiguous()
     for i in range(D):
         d.Whh[i] = whh[i].data_ptr()
+        if whhT is not None:
+            assert whhT[i].dtype == torch.bfloat16 and whhT[i].is_contiguous() and whhT[i].shape == (H, 4 * H)
+            d.WhhT[i] = whhT[i].data_ptr()
         d.db_ih[i] = db_ih[i].data_ptr()
         d.db_hh[i] = db_hh[i].data_ptr() if db_hh is not None else None
     d.accumulate = int(accumulate)

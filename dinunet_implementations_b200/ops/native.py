@@ -190,7 +190,7 @@ class LstmFwdDesc(ctypes.Structure):
 
 class LstmBwdDesc(ctypes.Structure):
     _fields_ = [
-        ("P", ctypes.c_void_p), ("C", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2),
+        ("P", ctypes.c_void_p), ("C", ctypes.c_void_p), ("Whh", ctypes.c_void_p * 2), ("WhhT", ctypes.c_void_p * 2),
         ("dHmean", ctypes.c_void_p), ("dP", ctypes.c_void_p),
         ("db_ih", ctypes.c_void_p * 2), ("db_hh", ctypes.c_void_p * 2),
         ("dbg", ctypes.c_void_p),

@@ -134,6 +134,8 @@ typedef struct DnbLstmBwdDesc {
     const float* P;          /* [S*B, D*4H] pre-activations from the forward */
     const float* C;          /* [D, S, B, H] */
     const void* Whh[2];
+    const void* WhhT[2];     /* optional bf16 [H, 4H] = Whh transposed: lets the kernel fill its tensor-memory operand
+                              * straight from global memory instead of transposing the slice in shared memory */
     const float* dHmean;     /* [B, D*H] gradient w.r.t. Hmean */
     void* dP;                /* [S*B, D*4H] bf16 out: gradient w.r.t. the pre-activations */
     float* db_ih[2];         /* per direction [4H] bias gradient (required) */

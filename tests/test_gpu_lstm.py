@@ -47,7 +47,11 @@ def test_lstm_forward_and_backward(B, S, H, D):
         db_ih = [torch.zeros(4 * H, device="cuda") for _ in range(D)]
         db_hh = [torch.zeros(4 * H, device="cuda") for _ in range(D)]
         dP = lstm_backward(px, C, whh, G.contiguous(), B, S, H, D, db_ih, db_hh)
+        # same launch with the recurrent weights handed over pre-transposed (no in-kernel transposition)
+        db2 = [torch.zeros(4 * H, device="cuda") for _ in range(D)]
+        dP2 = lstm_backward(px, C, whh, G.contiguous(), B, S, H, D, db2, None, whhT=[w.t().contiguous() for w in whh])
         torch.cuda.synchronize()
+        assert torch.equal(dP2, dP) and all(torch.allclose(x, y, atol=1e-6, rtol=1e-5) for x, y in zip(db2, db_ih))
         dPf = dP.float()
         enc_rows = enc.detach().permute(1, 0, 2).reshape(S * B, -1)
         for d, cell in enumerate(lstm.lstms):
