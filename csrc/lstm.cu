@@ -7,16 +7,18 @@
 //
 // The input projection i2h(x_t) for all timesteps is one big GEMM done beforehand (K5a,
 // csrc/gemm.cu); these kernels run only the serial part.  One thread-block cluster handles
-// one (direction, batch tile of 16).  CTA c of the H/32 CTAs in the cluster owns hidden units
+// one (direction, batch sub-tile).  CTA c of the H/32 CTAs in the cluster owns hidden units
 // [32c, 32c+32): all four gates of those units, their cell state, and the matching slice of
-// W_hh, resident in shared memory for the whole sequence.
+// W_hh, resident in TENSOR MEMORY for the whole sequence (tcgen05.mma with the A operand in TMEM:
+// with N = 16 an smem A operand is re-read from shared memory by every K=16 instruction, 4 KB at
+// 128 B/clk, which bounded the recurrent GEMM).
 //
 // forward, per step (all-gather design):
 //   tcgen05.mma  D[128 gate rows, 16 batch] = W_hh[own rows, 0:H] · h_{t-1}[batch, 0:H]ᵀ
-//                (A = weight slice, K-major SW128 smem; B = h_{t-1}, K-major un-swizzled smem, every
-//                CTA holds the full vector; accumulator in TMEM; issued under elect.sync)
+//                (A = weight slice in TMEM; B = h_{t-1}, K-major un-swizzled smem, every CTA holds the
+//                full vector; accumulator in TMEM; issued under elect.sync)
 //   epilogue     tcgen05.ld → + i2h(x_t) + b_hh → σ(σ(·)) / tanh → cell update in registers →
-//                the CTA's h_t slice (bf16, two contiguous 512-byte runs in the operand layout) is
+//                the CTA's h_t slice (bf16, contiguous 512-byte runs in the operand layout) is
 //                staged and pushed into EVERY cluster CTA's next-step B operand with cp.async.bulk
 //                (shared::cta → shared::cluster); each copy does one complete_tx on the receiver's
 //                mbarrier, whose completion releases the receiver's next MMA.  No cluster barrier and
@@ -24,21 +26,30 @@
 // backward, per step (reduce-scatter design):
 //   tcgen05.mma  partial dh[H units, 16 batch] = W_hhᵀ[0:H, own gate rows] · dP_t[batch, own rows]ᵀ
 //                (K = this CTA's 128 gate rows, so the B operand is purely local)
-//   exchange     each warp stages its 32-unit block of the partial (2 KB) and bulk-copies it to the
+//   exchange     each warp stages its 32-unit block of the partial (bf16) and bulk-copies it to the
 //                CTA that owns those units → that CTA's mbarrier completes when all H/32 blocks have
-//                landed → owner sums them, adds the upstream gradient, back-propagates through the cell
-//                and the double sigmoid, emits dP_{t-1} (bf16: to global memory for the weight-gradient
+//                landed → owner sums them in fp32, adds the upstream gradient, back-propagates through the
+//                cell and the double sigmoid, emits dP_{t-1} (bf16: to global memory for the weight-gradient
 //                GEMMs, and to its local B operand for the next step).
 // Global loads for step t±1 and the global stores of step t∓1 are software-pipelined around the MMA.
-// Activations use tanh.approx (one MUFU op per sigmoid/tanh).
+//
+// Batch sub-tiling: the tensor-core tile is always N = 16 batch columns, but a cluster may own only
+// NBE = 8 of them (the others stay zero and are never computed on or exchanged).  With few batch rows
+// the kernels are bound by per-step latency — per-thread epilogue work, and the ~17-21 B/clk per SM of
+// the SM-to-SM network that carries h_t / the partial dh — both proportional to NBE, while most of the
+// 148 SMs idle.  Halving NBE doubles the number of clusters and halves both terms.
+//
+// Activations use tanh.approx (one MUFU op per sigmoid/tanh); the second sigmoid of the reference's
+// double-sigmoid gates runs on the FMA pipe (polynomial, its argument is in [0,1]).
 #include "common.cuh"
+#include <cstdlib>
 #include "../include/dinunet_b200.h"
 
 void dnb_count_launch(int n);
 
 namespace {
 
-constexpr int NB = 16;           // batch tile = MMA N
+constexpr int NB = 16;           // MMA N (batch columns of the operand tile)
 constexpr int U = 32;            // hidden units per CTA
 constexpr int kThreads = 128;
 constexpr int kMaxCtas = 8;
@@ -54,7 +65,7 @@ struct FwdArgs {
     float* Hmean;                    // [B, D*H]
     float* hT;                       // [B, D*H]
     float* cT;                       // [B, D*H]
-    long long* dbg;                  // optional: clock64 stamps of one mid-sequence step (profiling aid)
+    long long* dbg;                  // optional: mean clock64 stamps per phase (profiling aid)
     int B, S, H, D;
 };
 
@@ -72,6 +83,48 @@ struct BwdArgs {
     int B, S, H, D;
 };
 
+// per-thread roles of the cell update for a batch sub-tile of NBE rows: every thread owns UPT consecutive
+// hidden units of one batch row (NBE x 32 units over 128 threads)
+template <int NBE> struct Roles {
+    static constexpr int UPT = NBE / 4;          // units per thread: 4 (NBE 16) or 2 (NBE 8)
+    static constexpr int TPR = U / UPT;          // threads per batch row: 8 or 16
+};
+
+// small fixed-size vector moves (N = 2 or 4)
+template <int N> __device__ __forceinline__ void ldv(float (&d)[N], const float* p) {
+    if constexpr (N == 4) {
+        const float4 v = *reinterpret_cast<const float4*>(p);
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    } else {
+        const float2 v = *reinterpret_cast<const float2*>(p);
+        d[0] = v.x; d[1] = v.y;
+    }
+}
+template <int N> __device__ __forceinline__ void stv(float* p, const float (&s)[N]) {
+    if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(s[0], s[1], s[2], s[3]);
+    else *reinterpret_cast<float2*>(p) = make_float2(s[0], s[1]);
+}
+template <int N> struct BfPack;     // N bf16 values as one 4- or 8-byte word
+template <> struct BfPack<4> { uint2 w; };
+template <> struct BfPack<2> { uint32_t w; };
+template <int N> __device__ __forceinline__ BfPack<N> pack_bf(const float (&s)[N]) {
+    BfPack<N> r;
+    if constexpr (N == 4) { r.w.x = dnb::pack_bf16x2(s[0], s[1]); r.w.y = dnb::pack_bf16x2(s[2], s[3]); }
+    else r.w = dnb::pack_bf16x2(s[0], s[1]);
+    return r;
+}
+template <int N> __device__ __forceinline__ BfPack<N> zero_bf() {
+    BfPack<N> r;
+    if constexpr (N == 4) r.w = make_uint2(0, 0); else r.w = 0;
+    return r;
+}
+template <int N> __device__ __forceinline__ void st_bf(void* p, const BfPack<N>& v) {
+    if constexpr (N == 4) *reinterpret_cast<uint2*>(p) = v.w; else *reinterpret_cast<uint32_t*>(p) = v.w;
+}
+template <int N> __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&v)[N]) {
+    if constexpr (N == 16) dnb::tmem_ld_32x16(taddr, v); else dnb::tmem_ld_32x8(taddr, v);
+}
+
 // byte offset of element (row, k) inside a K-major SWIZZLE_128B operand made of 64-wide k-blocks
 __device__ __forceinline__ uint32_t sw128_off(int rows_per_block, int row, int k) {
     const int kb = k >> 6, kk = k & 63;
@@ -80,7 +133,6 @@ __device__ __forceinline__ uint32_t sw128_off(int rows_per_block, int row, int k
 }
 
 __device__ __forceinline__ float dsig(float y) { return y * (1.f - y); }
-
 // Profiling aid: per-phase cycle counts of one thread (block 0, thread 0), averaged over the middle half
 // of the sequence in registers and written once at the end (dbg[i] = mean clock at stamp i relative to
 // stamp 0, so consecutive differences are mean phase lengths).
@@ -111,20 +163,22 @@ __device__ __forceinline__ constexpr uint64_t koff_b(int k) { return (uint64_t)(
 __device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(k * (256 / 16)); }
 
 // ------------------------------------------------------------------------------------ forward
+template <int NBE>
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
+    constexpr int UPT = Roles<NBE>::UPT, TPR = Roles<NBE>::TPR, NG = NBE / 8;   // NG = 8-row groups exchanged
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
     const int H = a.H;
     // h_{t-1} as the MMA B operand: K-major, NO swizzle — 8-row x 16-byte core matrices, consecutive
     // k-chunks 128 B apart, the two 8-row groups h_sbo apart.  In this layout the 32 hidden units a CTA
-    // produces are two contiguous 512-byte runs (one per row group), so a CTA hands its slice to a peer
-    // with two bulk copies instead of 64 per-thread 16-byte stores.
+    // produces are one contiguous 512-byte run per row group, so a CTA hands its slice to a peer with
+    // NG bulk copies instead of per-thread 16-byte stores.  Row groups >= NG stay zero.
     const int h_sbo = (H / 8) * 128;                 // bytes between the two 8-row groups
     const int h_bytes = NB * H * 2;                  // one h buffer (= 2 * h_sbo)
     uint8_t* sH = smem;                              // two buffers
-    float* sAct = reinterpret_cast<float*>(sH + 2 * h_bytes);   // [4][NB][U]
-    uint8_t* sStage = reinterpret_cast<uint8_t*>(sAct + 4 * NB * U);   // [2 parity][2 row groups][512 B] own h slice
-    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStage + 2 * 1024);
+    float* sAct = reinterpret_cast<float*>(sH + 2 * h_bytes);   // [4][NBE][U]
+    uint8_t* sStage = reinterpret_cast<uint8_t*>(sAct + 4 * NBE * U);   // [2 parity][NG row groups][512 B] own h slice
+    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStage + 2 * NG * 512);
     uint64_t* hbar = mma_bar + 1;                    // [2]: "h_{t-1} has fully arrived in buffer p"
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(hbar + 2);
 
@@ -135,10 +189,10 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     const int ncta = dnb::cluster_nctarank();
     const int cta = dnb::cluster_ctarank();
     const int cid = blockIdx.x / ncta;
-    const int dir = cid % a.D, b0 = (cid / a.D) * NB;
+    const int dir = cid % a.D, b0 = (cid / a.D) * NBE;
     const size_t ldp = (size_t)a.D * 4 * H, ldh = (size_t)a.D * H;
-    const int nvalid = min(NB, a.B - b0);            // real batch rows in this tile
-    const uint32_t h_tx_bytes = (uint32_t)(NB * H * 2);
+    const int nvalid = min(NBE, a.B - b0);           // real batch rows in this tile
+    const uint32_t h_tx_bytes = (uint32_t)(NBE * H * 2);
 
     // ---- one-time: zero h_{-1}; the weight slice goes to tensor memory once the allocation exists
     for (int idx = tid; idx < 2 * h_bytes / 16; idx += kThreads)
@@ -164,11 +218,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
 
     // epilogue-1 role: thread = gate row (q = warp, u = lane)
     const int grow = warp * H + cta * U + lane;
-    // A operand = this CTA's 128 gate rows of W_hh, resident in TENSOR MEMORY for the whole sequence:
-    // lane = gate row (the same row this thread owns in the epilogue), 32-bit column j = k-elements
-    // 2j, 2j+1.  With N = 16 an smem A operand makes every K=16 instruction re-read a 4 KB tile from
-    // shared memory (>= 32 cycles at 128 B/clk — the recurrent GEMM was bound by exactly that); from
-    // TMEM the same instruction issues at the tensor pipe's own rate.
+    // A operand: lane = gate row (the same row this thread owns in the epilogue), 32-bit column j =
+    // k-elements 2j, 2j+1
     {
         const uint4* wrow = reinterpret_cast<const uint4*>(a.Whh[dir] + (size_t)grow * H);
         const uint32_t a_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + kTmemA;
@@ -191,22 +242,24 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     dnb::cluster_sync_all();       // every CTA's buffers and barriers exist before anyone writes remotely
     dnb::tc_fence_after();
     const float bias = a.bhh[dir][grow];
-    // epilogue-2 role: thread = (batch b2, 4 consecutive units)
-    const int b2 = tid >> 3, ug = tid & 7;
+    // epilogue-2 role: thread = (batch row b2, UPT consecutive units from u0)
+    const int b2 = tid / TPR, u0 = (tid % TPR) * UPT;
     const bool b2_ok = b2 < nvalid;
-    float c[4] = {0.f, 0.f, 0.f, 0.f}, hsum[4] = {0.f, 0.f, 0.f, 0.f}, hlast[4] = {0.f, 0.f, 0.f, 0.f};
+    float c[UPT], hsum[UPT], hlast[UPT];
+#pragma unroll
+    for (int j = 0; j < UPT; ++j) c[j] = hsum[j] = hlast[j] = 0.f;
 
     // pointers walk the sequence in processing order (reverse direction: time runs backwards)
     const long long row_step = dir ? -(long long)a.B : (long long)a.B;
     const long long row_first = (long long)(dir ? a.S - 1 : 0) * a.B + b0;
     float* px_ptr = a.PX + (size_t)row_first * ldp + (size_t)dir * 4 * H + grow;          // + b*ldp
     const long long px_step = row_step * (long long)ldp;
-    float* c_ptr = a.C + (((size_t)dir * a.S) * a.B + b0 + b2) * H + cta * U + ug * 4;     // step stride B*H
+    float* c_ptr = a.C + (((size_t)dir * a.S) * a.B + b0 + b2) * H + cta * U + u0;         // step stride B*H
     const size_t c_step = (size_t)a.B * H;
-    __nv_bfloat16* hp_ptr = a.Hprev + (size_t)(row_first + b2) * ldh + (size_t)dir * H + cta * U + ug * 4;
+    __nv_bfloat16* hp_ptr = a.Hprev + (size_t)(row_first + b2) * ldh + (size_t)dir * H + cta * U + u0;
     const long long hp_step = row_step * (long long)ldh;
 
-    if (b2_ok) *reinterpret_cast<uint2*>(hp_ptr) = make_uint2(0, 0);      // h_{-1} = 0 in the saved sequence
+    if (b2_ok) st_bf<UPT>(hp_ptr, zero_bf<UPT>());      // h_{-1} = 0 in the saved sequence
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
     // broadcast from lane 0 so the compiler keeps descriptors / TMEM address in uniform registers
@@ -215,21 +268,20 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     const uint64_t db_base0 = dnb::umma_desc_k_noswizzle(sH_u, 128, h_sbo);
     const uint64_t db_base1 = dnb::umma_desc_k_noswizzle(sH_u + h_bytes, 128, h_sbo);
     const int ksteps = H / 16;
-    // this thread's 8 bytes (4 units of batch row b2) inside the staged slice: [row group][k-chunk][row][16 B]
-    const uint32_t stage_off = (uint32_t)((b2 >> 3) * 512 + (ug >> 1) * 128 + (b2 & 7) * 16 + (ug & 1) * 8);
+    // this thread's UPT units of batch row b2 inside the staged slice: [row group][k-chunk][row][16 B]
+    const uint32_t stage_off = (uint32_t)((b2 >> 3) * 512 + (u0 >> 3) * 128 + (b2 & 7) * 16 + (u0 & 7) * 2);
     const uint32_t sStage_u = __shfl_sync(0xffffffffu, dnb::smem_u32(sStage), 0);
     const uint32_t hbar_u = __shfl_sync(0xffffffffu, dnb::smem_u32(&hbar[0]), 0);
     const uint32_t slice_off = (uint32_t)(cta * 4 * 128);     // where this CTA's 4 k-chunks sit inside a row group
 
     // Software pipeline: i2h(x) for step t+1 is fetched during step t; the global stores of step t
     // (saved pre-activations, cell state, h for the weight-gradient GEMM) are issued at the start of
-    // step t+1 while the MMA runs.  Cross-CTA hand-off of h_t is st.async + mbarrier complete_tx:
-    // no fences, no cluster barrier on the critical path.
-    float px_next[NB];
+    // step t+1, while h_t is still in flight between the CTAs.
+    float px_next[NBE];
 #pragma unroll
-    for (int b = 0; b < NB; ++b) px_next[b] = (b < nvalid) ? px_ptr[(size_t)b * ldp] : 0.f;
-    float pst[NB];
-    uint2 hb_prev = make_uint2(0, 0);
+    for (int b = 0; b < NBE; ++b) px_next[b] = (b < nvalid) ? px_ptr[(size_t)b * ldp] : 0.f;
+    float pst[NBE];
+    BfPack<UPT> hb_prev = zero_bf<UPT>();
 
     DNB_STAMP_DECL;
     if (mark) a.dbg[13] = clock64();
@@ -237,27 +289,27 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
         stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
-        float px[NB];
+        float px[NBE];
 #pragma unroll
-        for (int b = 0; b < NB; ++b) px[b] = px_next[b];
+        for (int b = 0; b < NBE; ++b) px[b] = px_next[b];
 
         // ---- first, while h_{t-1} is still in flight between the CTAs: deferred stores of step t-1 and
         // the prefetch of step t+1 (the issuing warp does this BEFORE it waits for h, so neither the
-        // exchange latency nor the MMA ever waits for these ~35 memory instructions)
+        // exchange latency nor the MMA ever waits for these memory instructions)
         if (t > 0) {
             float* pprev = px_ptr - px_step;
 #pragma unroll
-            for (int b = 0; b < NB; ++b)
+            for (int b = 0; b < NBE; ++b)
                 if (b < nvalid) pprev[(size_t)b * ldp] = pst[b];
             if (b2_ok) {
-                *reinterpret_cast<float4*>(c_ptr - c_step) = make_float4(c[0], c[1], c[2], c[3]);
-                *reinterpret_cast<uint2*>(hp_ptr) = hb_prev;          // h_{t-1} at the time row of step t
+                stv<UPT>(c_ptr - c_step, c);
+                st_bf<UPT>(hp_ptr, hb_prev);              // h_{t-1} at the time row of step t
             }
         }
         if (t + 1 < a.S) {
             const float* pn = px_ptr + px_step;
 #pragma unroll
-            for (int b = 0; b < NB; ++b) px_next[b] = (b < nvalid) ? pn[(size_t)b * ldp] : 0.f;
+            for (int b = 0; b < NBE; ++b) px_next[b] = (b < nvalid) ? pn[(size_t)b * ldp] : 0.f;
         }
         DNB_STAMP(1);
         if (warp == 0) {
@@ -282,56 +334,53 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         dnb::mbar_wait(mma_bar, t & 1);
         dnb::tc_fence_after();
         DNB_STAMP(4);
-        uint32_t acc[NB];
-        dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
+        uint32_t acc[NBE];
+        tmem_ld_cols<NBE>(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
         dnb::tmem_ld_wait();
         DNB_STAMP(5);
-        // 16 independent activation chains per thread; the gate type is warp-uniform, so the branch
+        // NBE independent activation chains per thread; the gate type is warp-uniform, so the branch
         // sits outside the unrolled loop and the MUFU ops of different batch columns overlap
 #pragma unroll
-        for (int b = 0; b < NB; ++b) pst[b] = __uint_as_float(acc[b]) + px[b] + bias;   // saved for BPTT
-        float* act_row = sAct + warp * NB * U + lane;
+        for (int b = 0; b < NBE; ++b) pst[b] = __uint_as_float(acc[b]) + px[b] + bias;   // saved for BPTT
+        float* act_row = sAct + warp * NBE * U + lane;
         if (warp < 3) {
 #pragma unroll
-            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::sigmoid01_poly(dnb::sigmoid_fast(pst[b]));
+            for (int b = 0; b < NBE; ++b) act_row[b * U] = dnb::sigmoid01_poly(dnb::sigmoid_fast(pst[b]));
         } else {
 #pragma unroll
-            for (int b = 0; b < NB; ++b) act_row[b * U] = dnb::tanh_fast(pst[b]);
+            for (int b = 0; b < NBE; ++b) act_row[b * U] = dnb::tanh_fast(pst[b]);
         }
         DNB_STAMP(6);
         dnb::tc_fence_before();
         __syncthreads();
         DNB_STAMP(7);
 
-        // cell update: (b2, units ug*4 .. ug*4+3)
-        const float4 gi = *reinterpret_cast<const float4*>(sAct + (0 * NB + b2) * U + ug * 4);
-        const float4 gf = *reinterpret_cast<const float4*>(sAct + (1 * NB + b2) * U + ug * 4);
-        const float4 go = *reinterpret_cast<const float4*>(sAct + (2 * NB + b2) * U + ug * 4);
-        const float4 gg = *reinterpret_cast<const float4*>(sAct + (3 * NB + b2) * U + ug * 4);
-        const float iv[4] = {gi.x, gi.y, gi.z, gi.w}, fv[4] = {gf.x, gf.y, gf.z, gf.w};
-        const float ov[4] = {go.x, go.y, go.z, go.w}, gv[4] = {gg.x, gg.y, gg.z, gg.w};
+        // cell update: (b2, units u0 .. u0+UPT-1)
+        float iv[UPT], fv[UPT], ov[UPT], gv[UPT];
+        ldv<UPT>(iv, sAct + (0 * NBE + b2) * U + u0);
+        ldv<UPT>(fv, sAct + (1 * NBE + b2) * U + u0);
+        ldv<UPT>(ov, sAct + (2 * NBE + b2) * U + u0);
+        ldv<UPT>(gv, sAct + (3 * NBE + b2) * U + u0);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < UPT; ++j) {
             c[j] = fv[j] * c[j] + iv[j] * gv[j];
             hlast[j] = ov[j] * dnb::tanh_fast(c[j]);
             hsum[j] += hlast[j];
         }
-        uint2 hb;
-        hb.x = dnb::pack_bf16x2(hlast[0], hlast[1]);
-        hb.y = dnb::pack_bf16x2(hlast[2], hlast[3]);
+        const BfPack<UPT> hb = pack_bf<UPT>(hlast);
         hb_prev = hb;
         DNB_STAMP(8);
         if (t + 1 < a.S) {
-            // stage the slice, then (one elected thread) two 512-byte bulk copies per peer: data lands in
-            // every CTA's next B operand and counts on that CTA's "h arrived" barrier (async proxy on both
-            // ends: no cluster barrier, and one mbarrier update per copy instead of one per 16 bytes)
+            // stage the slice, then (one elected thread per warp) one 512-byte bulk copy per row group and
+            // peer: data lands in every CTA's next B operand and counts on that CTA's "h arrived" barrier
+            // (async proxy on both ends: no cluster barrier, one mbarrier update per copy)
             const int par = (t + 1) & 1;
-            *reinterpret_cast<uint2*>(sStage + par * 1024 + stage_off) = hb;
+            st_bf<UPT>(sStage + par * NG * 512 + stage_off, hb);
             dnb::fence_proxy_async_smem();
             __syncthreads();
             DNB_STAMP(9);
-            if (dnb::elect_one()) {                       // one thread per warp; warp w serves peers w, w+4
-                const uint32_t src = sStage_u + par * 1024;
+            if (dnb::elect_one()) {                       // warp w serves peers w, w+4
+                const uint32_t src = sStage_u + par * NG * 512;
                 const uint32_t dst = sH_u + par * h_bytes + slice_off;
                 const uint32_t bar = hbar_u + par * 8;
 #pragma unroll
@@ -339,8 +388,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
                     const int peer = warp + 4 * pp;
                     if (peer < ncta) {
                         const uint32_t rbar = dnb::mapa(bar, peer);
-                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(dst, peer), src, 512, rbar);
-                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(dst + h_sbo, peer), src + 512, 512, rbar);
+#pragma unroll
+                        for (int g = 0; g < NG; ++g)
+                            dnb::bulk_copy_smem_to_cluster(dnb::mapa(dst + g * h_sbo, peer), src + g * 512, 512, rbar);
                     }
                 }
             }
@@ -357,17 +407,20 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     {
         float* pprev = px_ptr - px_step;
 #pragma unroll
-        for (int b = 0; b < NB; ++b)
+        for (int b = 0; b < NBE; ++b)
             if (b < nvalid) pprev[(size_t)b * ldp] = pst[b];
-        if (b2_ok) *reinterpret_cast<float4*>(c_ptr - c_step) = make_float4(c[0], c[1], c[2], c[3]);
+        if (b2_ok) stv<UPT>(c_ptr - c_step, c);
     }
 
     if (b2_ok) {
-        const size_t o = (size_t)(b0 + b2) * ldh + dir * H + cta * U + ug * 4;
+        const size_t o = (size_t)(b0 + b2) * ldh + dir * H + cta * U + u0;
         const float inv = 1.f / (float)a.S;
-        *reinterpret_cast<float4*>(a.Hmean + o) = make_float4(hsum[0] * inv, hsum[1] * inv, hsum[2] * inv, hsum[3] * inv);
-        if (a.hT) *reinterpret_cast<float4*>(a.hT + o) = make_float4(hlast[0], hlast[1], hlast[2], hlast[3]);
-        if (a.cT) *reinterpret_cast<float4*>(a.cT + o) = make_float4(c[0], c[1], c[2], c[3]);
+        float hm[UPT];
+#pragma unroll
+        for (int j = 0; j < UPT; ++j) hm[j] = hsum[j] * inv;
+        stv<UPT>(a.Hmean + o, hm);
+        if (a.hT) stv<UPT>(a.hT + o, hlast);
+        if (a.cT) stv<UPT>(a.cT + o, c);
     }
     dnb::tc_fence_before();
     __syncthreads();
@@ -380,19 +433,22 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
 }
 
 // ------------------------------------------------------------------------------------ backward
+template <int NBE>
 __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) {
+    constexpr int UPT = Roles<NBE>::UPT, TPR = Roles<NBE>::TPR;
+    constexpr int BLK = NBE * U;                         // elements of one partial-dh block: [batch row][unit]
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
     const int H = a.H;
     const int MT = (H + 127) / 128;                      // M tiles over hidden units
     const int w_pitch = H * 2 + 16;                      // staging row pitch (+16 B: conflict-free 16-byte stores)
+    const int ncta = dnb::cluster_nctarank();
     uint8_t* sW = smem;                                  // one-time staging of the weight slice [128 gate rows][H]
     uint8_t* sB = smem + 128 * w_pitch;                  // dP_t slice: [NB rows][128 k] = 2 k-blocks x NB x 128 B
-    float* sRed = reinterpret_cast<float*>(sB + 2 * NB * 128);   // [2][ncta][U][NB]
-    const int ncta = dnb::cluster_nctarank();
-    float* sDb = sRed + 2 * ncta * U * NB;               // [128] bias-gradient reduction
-    float* sStg = sDb + 128;                             // [2 parity][4 warps][2 tiles][U*NB] outgoing partial blocks
-    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sStg + 2 * 4 * 2 * U * NB);
+    __nv_bfloat16* sRed = reinterpret_cast<__nv_bfloat16*>(sB + 2 * NB * 128);   // [2 parity][ncta sources][BLK] incoming
+    __nv_bfloat16* sStg = sRed + 2 * ncta * BLK;         // [2 parity][4 warps][2 tiles][BLK] outgoing
+    float* sDb = reinterpret_cast<float*>(sStg + 2 * 4 * 2 * BLK);   // [4 warps + 1][128] bias-gradient reduction
+    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(sDb + 5 * 128);
     uint64_t* rbar = mma_bar + 1;                        // [2]: "all partial dh blocks of round n arrived"
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rbar + 2);
 
@@ -402,17 +458,16 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int cta = dnb::cluster_ctarank();
     const int cid = blockIdx.x / ncta;
-    const int dir = cid % a.D, b0 = (cid / a.D) * NB;
+    const int dir = cid % a.D, b0 = (cid / a.D) * NBE;
     const size_t ldp = (size_t)a.D * 4 * H, ldh = (size_t)a.D * H;
-    const int nvalid = min(NB, a.B - b0);
-    const uint32_t red_tx_bytes = (uint32_t)(ncta * U * NB * 4);
+    const int nvalid = min(NBE, a.B - b0);
+    const uint32_t red_tx_bytes = (uint32_t)(ncta * BLK * 2);
     const int rounds = a.S - 1;
 
-    // ---- one-time: this CTA's 128 gate rows of W_hh -> shared memory (row-major, coalesced 16-byte
-    // loads); transposed into tensor memory below, once the allocation exists
+    // ---- one-time: zero the B operand (rows >= NBE stay zero); without pre-transposed weights, stage this
+    // CTA's 128 gate rows of W_hh in shared memory (row-major, coalesced 16-byte loads) for the transposition
     for (int idx = tid; idx < (2 * NB * 128) / 16; idx += kThreads)
         reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
-    sDb[tid] = 0.f;
     const __nv_bfloat16* W = a.Whh[dir];
     const __nv_bfloat16* WT = a.WhhT[dir];
     if (WT == nullptr) {
@@ -451,10 +506,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    // A operand in TENSOR MEMORY (see the forward kernel): tile mt, lane m = hidden unit mt*128 + m,
-    // 32-bit column j2 = W_hh[own gate row 2*j2, unit] | W_hh[own gate row 2*j2+1, unit] << 16 — i.e.
-    // W_hh^T restricted to this CTA's gate rows, K = 128.  Thread m reads column `unit` of the staged
-    // slice (consecutive lanes -> consecutive 2-byte elements: conflict-free).
+    // A operand in TENSOR MEMORY: tile mt, lane m = hidden unit mt*128 + m, 32-bit column j2 =
+    // W_hh[own gate row 2*j2, unit] | W_hh[own gate row 2*j2+1, unit] << 16 — i.e. W_hh^T restricted to
+    // this CTA's gate rows, K = 128.
     for (int mt = 0; mt < MT; ++mt) {
         const int unit = mt * 128 + tid;
         const uint32_t a_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + kTmemA + mt * 64;
@@ -475,6 +529,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             }
             continue;
         }
+        // in-kernel transposition: thread m reads column `unit` of the staged slice (consecutive lanes ->
+        // consecutive 2-byte elements: conflict-free)
 #pragma unroll 2
         for (int c = 0; c < 8; ++c) {
             uint32_t r[8];
@@ -496,31 +552,34 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     dnb::cluster_sync_all();
     dnb::tc_fence_after();
 
-    const int b2 = tid >> 3, ug = tid & 7;
+    // thread role: (batch row b2, UPT consecutive units from u0)
+    const int b2 = tid / TPR, u0 = (tid % TPR) * UPT;
     const bool b_ok = b2 < nvalid;
-    const int ucol = cta * U + ug * 4;                  // first of this thread's 4 hidden units
-    float dc[4] = {0.f, 0.f, 0.f, 0.f};
-    float dh_out[4] = {0.f, 0.f, 0.f, 0.f};
+    const int ucol = cta * U + u0;                      // first of this thread's hidden units
+    float dc[UPT], dh_out[UPT];
+#pragma unroll
+    for (int j = 0; j < UPT; ++j) dc[j] = dh_out[j] = 0.f;
     if (b_ok) {
-        const float4 v = *reinterpret_cast<const float4*>(a.dHmean + (size_t)(b0 + b2) * ldh + dir * H + ucol);
+        ldv<UPT>(dh_out, a.dHmean + (size_t)(b0 + b2) * ldh + dir * H + ucol);
         const float inv = 1.f / (float)a.S;
-        dh_out[0] = v.x * inv; dh_out[1] = v.y * inv; dh_out[2] = v.z * inv; dh_out[3] = v.w * inv;
+#pragma unroll
+        for (int j = 0; j < UPT; ++j) dh_out[j] *= inv;
     }
-    float dbacc[4][4];
+    float dbacc[4][UPT];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dbacc[q][j] = 0.f;
+        for (int j = 0; j < UPT; ++j) dbacc[q][j] = 0.f;
 
     const uint32_t idesc = dnb::umma_idesc_bf16(128, NB);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t db_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sB), 0));
-    // where this warp's partial-dh blocks go: tile mt of warp w belongs to CTA mt*4 + w
-    const uint32_t red_blk[2] = {dnb::smem_u32(sRed + (size_t)cta * U * NB),
-                                 dnb::smem_u32(sRed + (size_t)ncta * U * NB + (size_t)cta * U * NB)};
+    // where this CTA's partial-dh blocks land in an owner's sRed: [parity][source = this CTA]
+    const uint32_t red_blk[2] = {dnb::smem_u32(sRed + (size_t)cta * BLK),
+                                 dnb::smem_u32(sRed + (size_t)ncta * BLK + (size_t)cta * BLK)};
     const uint32_t rbar_local[2] = {dnb::smem_u32(&rbar[0]), dnb::smem_u32(&rbar[1])};
-    const uint32_t sB_off[4] = {sw128_off(NB, b2, 0 * U + ug * 4), sw128_off(NB, b2, 1 * U + ug * 4),
-                                sw128_off(NB, b2, 2 * U + ug * 4), sw128_off(NB, b2, 3 * U + ug * 4)};
+    const uint32_t sB_off[4] = {sw128_off(NB, b2, 0 * U + u0), sw128_off(NB, b2, 1 * U + u0),
+                                sw128_off(NB, b2, 2 * U + u0), sw128_off(NB, b2, 3 * U + u0)};
 
     // pointers walk the sequence backwards in processing order
     const long long row_step = dir ? (long long)a.B : -(long long)a.B;      // towards step t-1
@@ -532,17 +591,20 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const size_t c_step = (size_t)a.B * H;
 
     // Software pipeline (see forward): the saved state of step t-1 is fetched while step t is
-    // processed; dP_t goes to global memory one step late; the activation recompute (MUFU-heavy,
-    // independent of dh) overlaps the MMA and the DSMEM reduction.
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    float4 pq_n[4], cc_n, cp_n;
+    // processed; dP_t goes to global memory one step late; the activation recompute (independent of dh)
+    // overlaps the MMA and the DSMEM reduction.
+    float pq_n[4][UPT], cc_n[UPT], cp_n[UPT];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) pq_n[q] = b_ok ? *reinterpret_cast<const float4*>(p_ptr + q * H) : z4;
-    cc_n = b_ok ? *reinterpret_cast<const float4*>(c_ptr) : z4;
-    cp_n = (b_ok && a.S > 1) ? *reinterpret_cast<const float4*>(c_ptr - c_step) : z4;
-    uint2 dp_store[4];
+    for (int j = 0; j < UPT; ++j) cc_n[j] = cp_n[j] = pq_n[0][j] = pq_n[1][j] = pq_n[2][j] = pq_n[3][j] = 0.f;
+    if (b_ok) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) dp_store[q] = make_uint2(0, 0);
+        for (int q = 0; q < 4; ++q) ldv<UPT>(pq_n[q], p_ptr + q * H);
+        ldv<UPT>(cc_n, c_ptr);
+        if (a.S > 1) ldv<UPT>(cp_n, c_ptr - c_step);
+    }
+    BfPack<UPT> dp_store[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) dp_store[q] = zero_bf<UPT>();
 
     DNB_STAMP_DECL;
     if (mark) a.dbg[13] = clock64();
@@ -550,9 +612,13 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
         stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
-        float4 pq[4], cc = cc_n, cp = cp_n;
+        float pq[4][UPT], cv[UPT], cpv[UPT];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) pq[q] = pq_n[q];
+        for (int j = 0; j < UPT; ++j) {
+            cv[j] = cc_n[j]; cpv[j] = cp_n[j];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pq[q][j] = pq_n[q][j];
+        }
 
         const int n = a.S - 2 - t;                  // index of this MMA round (valid when t < S-1)
         if (t < a.S - 1 && warp == 0) {
@@ -575,26 +641,27 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         if (t < a.S - 1 && b_ok) {                   // dP of step t+1 -> global
             __nv_bfloat16* dprev = dp_ptr - p_step;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) *reinterpret_cast<uint2*>(dprev + q * H) = dp_store[q];
+            for (int q = 0; q < 4; ++q) st_bf<UPT>(dprev + q * H, dp_store[q]);
         }
-        if (t > 0) {
+        if (t > 0 && b_ok) {
             const float* pn = p_ptr + p_step;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) pq_n[q] = b_ok ? *reinterpret_cast<const float4*>(pn + q * H) : z4;
-            cc_n = b_ok ? *reinterpret_cast<const float4*>(c_ptr - c_step) : z4;
-            cp_n = (b_ok && t > 1) ? *reinterpret_cast<const float4*>(c_ptr - 2 * c_step) : z4;
+            for (int q = 0; q < 4; ++q) ldv<UPT>(pq_n[q], pn + q * H);
+            ldv<UPT>(cc_n, c_ptr - c_step);
+            if (t > 1) ldv<UPT>(cp_n, c_ptr - 2 * c_step);
+            else {
+#pragma unroll
+                for (int j = 0; j < UPT; ++j) cp_n[j] = 0.f;
+            }
         }
 
-        const float pi[4] = {pq[0].x, pq[0].y, pq[0].z, pq[0].w}, pf[4] = {pq[1].x, pq[1].y, pq[1].z, pq[1].w};
-        const float po[4] = {pq[2].x, pq[2].y, pq[2].z, pq[2].w}, pg[4] = {pq[3].x, pq[3].y, pq[3].z, pq[3].w};
-        const float cv[4] = {cc.x, cc.y, cc.z, cc.w}, cpv[4] = {cp.x, cp.y, cp.z, cp.w};
         // local Jacobian factors of the cell (recomputed from the saved pre-activations)
-        float k_i[4], k_f[4], k_g[4], k_h[4], k_tc[4], k_fg[4];
+        float k_i[UPT], k_f[UPT], k_g[UPT], k_h[UPT], k_tc[UPT], k_fg[UPT];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float si = dnb::sigmoid_fast(pi[j]), sf = dnb::sigmoid_fast(pf[j]), so = dnb::sigmoid_fast(po[j]);
+        for (int j = 0; j < UPT; ++j) {
+            const float si = dnb::sigmoid_fast(pq[0][j]), sf = dnb::sigmoid_fast(pq[1][j]), so = dnb::sigmoid_fast(pq[2][j]);
             const float i = dnb::sigmoid01_poly(si), f = dnb::sigmoid01_poly(sf), o = dnb::sigmoid01_poly(so);
-            const float g = dnb::tanh_fast(pg[j]);
+            const float g = dnb::tanh_fast(pq[3][j]);
             const float tc = dnb::tanh_fast(cv[j]);
             k_h[j] = o * (1.f - tc * tc);            // dh -> dc
             k_tc[j] = tc * dsig(o) * dsig(so);       // dp_o = dh  * k_tc
@@ -603,37 +670,37 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             k_g[j] = i * (1.f - g * g);              // dp_g = dct * k_g
             k_fg[j] = f;                             // dc_{t-1} = dct * f
         }
-
         // pin the recompute HERE (in the shadow of the MMA and of the exchange): without a use before the
         // waits the compiler sinks it behind them, onto the critical path
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < UPT; ++j)
             asm volatile("" ::"f"(k_i[j]), "f"(k_f[j]), "f"(k_g[j]), "f"(k_h[j]), "f"(k_tc[j]), "f"(k_fg[j]));
-        float dh[4] = {dh_out[0], dh_out[1], dh_out[2], dh_out[3]};
+        float dh[UPT];
+#pragma unroll
+        for (int j = 0; j < UPT; ++j) dh[j] = dh_out[j];
         DNB_STAMP(2);
         if (t < a.S - 1) {
             dnb::mbar_wait(mma_bar, n & 1);
             dnb::tc_fence_after();
             DNB_STAMP(3);
-            // Each warp owns a 32-unit x 16-batch block of the partial dh per tile.  It is staged in
-            // shared memory (16-byte chunks XOR-swizzled by unit so the owner's column reads spread over
-            // banks) and shipped to the owning CTA with ONE bulk copy = one complete_tx on its barrier
-            // (per-thread st.async cost one mbarrier update per 16 bytes, 768 per CTA and step).
-            uint32_t v[2][NB];
+            // Each warp owns a 32-unit x NBE-batch block of the partial dh per tile; tile mt of warp w
+            // belongs to CTA mt*4 + w.  Blocks travel as bf16 (the SM-to-SM network moves ~17-21 B/clk per
+            // SM — the exchange, not the MMA, bounds this kernel), laid out [batch row][unit] so that the
+            // owner reads its UPT units with one load per source; ONE bulk copy per block = one
+            // complete_tx on the owner's barrier.
+            uint32_t v[2][NBE];
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
-                if (mt < MT) dnb::tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v[mt]);
+                if (mt < MT) tmem_ld_cols<NBE>(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * NB, v[mt]);
             dnb::tmem_ld_wait();
             DNB_STAMP(4);
-            float* stg = sStg + (((n & 1) * 4 + warp) * 2) * U * NB;     // this warp's two blocks of round n
-            const int swz = (lane >> 2) & 3;
+            __nv_bfloat16* stg = sStg + (((n & 1) * 4 + warp) * 2) * BLK;     // this warp's two blocks of round n
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
-                if (mt < MT && mt * 4 + warp < ncta) {     // tile mt of warp w belongs to CTA mt*4 + w
+                if (mt < MT && mt * 4 + warp < ncta) {
 #pragma unroll
-                    for (int x = 0; x < 4; ++x)
-                        *reinterpret_cast<uint4*>(stg + mt * U * NB + lane * NB + ((x ^ swz) << 2)) =
-                            make_uint4(v[mt][4 * x], v[mt][4 * x + 1], v[mt][4 * x + 2], v[mt][4 * x + 3]);
+                    for (int b = 0; b < NBE; ++b)
+                        stg[mt * BLK + b * U + lane] = __float2bfloat16_rn(__uint_as_float(v[mt][b]));
                 }
             dnb::fence_proxy_async_smem();                 // one fence for both blocks
             __syncwarp();
@@ -643,29 +710,36 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
                 for (int mt = 0; mt < 2; ++mt)
                     if (mt < MT && mt * 4 + warp < ncta)
                         dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk[n & 1], mt * 4 + warp),
-                                                       dnb::smem_u32(stg + mt * U * NB), U * NB * 4,
+                                                       dnb::smem_u32(stg + mt * BLK), BLK * 2,
                                                        dnb::mapa(rbar_local[n & 1], mt * 4 + warp));
             }
             DNB_STAMP(6);
             dnb::tc_fence_before();
             dnb::mbar_wait(&rbar[n & 1], (n >> 1) & 1);      // all partial blocks for my units arrived
             DNB_STAMP(7);
-            const float* red_par = sRed + (size_t)(n & 1) * ncta * U * NB + (ug * 4) * NB +
-                                   ((((b2 >> 2) ^ (ug & 3)) << 2) | (b2 & 3));
-            float part[kMaxCtas][4];
+            const __nv_bfloat16* red_par = sRed + (size_t)(n & 1) * ncta * BLK + b2 * U + u0;
+            BfPack<UPT> part[kMaxCtas];
 #pragma unroll
-            for (int src = 0; src < kMaxCtas; ++src)       // constant offsets; all loads issued before the adds
+            for (int src = 0; src < kMaxCtas; ++src) {     // constant offsets; all loads issued before the adds
+                if (src < ncta) {
+                    if constexpr (UPT == 4) part[src].w = *reinterpret_cast<const uint2*>(red_par + src * BLK);
+                    else part[src].w = *reinterpret_cast<const uint32_t*>(red_par + src * BLK);
+                } else part[src] = zero_bf<UPT>();
+            }
 #pragma unroll
-                for (int j = 0; j < 4; ++j) part[src][j] = (src < ncta) ? red_par[(src * U + j) * NB] : 0.f;
-#pragma unroll
-            for (int src = 0; src < kMaxCtas; ++src)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) dh[j] += part[src][j];
+            for (int src = 0; src < kMaxCtas; ++src) {
+                if constexpr (UPT == 4) {
+                    dh[0] += __uint_as_float(part[src].w.x << 16); dh[1] += __uint_as_float(part[src].w.x & 0xFFFF0000u);
+                    dh[2] += __uint_as_float(part[src].w.y << 16); dh[3] += __uint_as_float(part[src].w.y & 0xFFFF0000u);
+                } else {
+                    dh[0] += __uint_as_float(part[src].w << 16); dh[1] += __uint_as_float(part[src].w & 0xFFFF0000u);
+                }
+            }
         }
         DNB_STAMP(8);
-        float dp[4][4];
+        float dp[4][UPT];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < UPT; ++j) {
             const float dct = dc[j] + dh[j] * k_h[j];
             dp[0][j] = dct * k_i[j];
             dp[1][j] = dct * k_f[j];
@@ -676,13 +750,11 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            uint2 pk;
-            pk.x = dnb::pack_bf16x2(dp[q][0], dp[q][1]);
-            pk.y = dnb::pack_bf16x2(dp[q][2], dp[q][3]);
+            const BfPack<UPT> pk = pack_bf<UPT>(dp[q]);
             dp_store[q] = pk;
-            *reinterpret_cast<uint2*>(sB + sB_off[q]) = pk;      // local B operand of the next (earlier) step
+            st_bf<UPT>(sB + sB_off[q], pk);               // local B operand of the next (earlier) step
 #pragma unroll
-            for (int j = 0; j < 4; ++j) dbacc[q][j] += dp[q][j];
+            for (int j = 0; j < UPT; ++j) dbacc[q][j] += dp[q][j];
         }
         DNB_STAMP(9);
         p_ptr += p_step;
@@ -699,26 +771,24 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     if (b_ok) {                                      // dP of step 0
         __nv_bfloat16* dprev = dp_ptr - p_step;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) *reinterpret_cast<uint2*>(dprev + q * H) = dp_store[q];
+        for (int q = 0; q < 4; ++q) st_bf<UPT>(dprev + q * H, dp_store[q]);
     }
 
-    // bias gradients: sum over the batch rows — lanes that share ug inside a warp by shuffles (rows 4w..4w+3),
-    // then the four warps through shared memory (sRed is free: every incoming round has been consumed).
-    // (16-way contended shared atomics here cost ~10 us per launch.)
+    // bias gradients: sum over the batch rows — lanes that share u0 inside a warp by shuffles, then the
+    // four warps through shared memory.  (16-way contended shared atomics here cost ~10 us per launch.)
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < UPT; ++j) {
             float v = dbacc[q][j];
-            v += __shfl_xor_sync(0xffffffffu, v, 8);
-            v += __shfl_xor_sync(0xffffffffu, v, 16);
-            if (lane < 8) sRed[warp * 128 + q * U + ug * 4 + j] = v;
+#pragma unroll
+            for (int o = TPR; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane < TPR) sDb[warp * 128 + q * U + u0 + j] = v;
         }
     __syncthreads();
-    sDb[tid] = sRed[tid] + sRed[128 + tid] + sRed[256 + tid] + sRed[384 + tid];
     {
         const int gr = (tid >> 5) * H + cta * U + (tid & 31);
-        const float v = sDb[tid];
+        const float v = sDb[tid] + sDb[128 + tid] + sDb[256 + tid] + sDb[384 + tid];
         // batch tiles of the same direction add into the same vector
         if (a.accumulate || gridDim.x > (unsigned)(ncta * a.D)) {
             atomicAdd(a.db_a[dir] + gr, v);
@@ -759,12 +829,70 @@ int launch_cluster(void (*kernel)(const Args), const Args& args, int grid, int n
     return 0;
 }
 
+// How many clusters of `ncta` CTAs (1 CTA per SM, kThreads threads, `smem` bytes) can be resident at once.
+template <typename Args>
+int max_active_clusters(void (*kernel)(const Args), int ncta, size_t smem) {
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(ncta, 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ncta;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
 int check_shape(int B, int S, int H, int D) {
     DNB_REQUIRE(B >= 1 && S >= 1, "lstm: empty batch/sequence");
     DNB_REQUIRE(D == 1 || D == 2, "lstm: directions must be 1 or 2");
     DNB_REQUIRE(H % 32 == 0 && H >= 32 && H <= 32 * kMaxCtas,
-                "lstm: per-direction hidden size must be a multiple of 32 in [32, %d] (got %d)", 32 * kMaxCtas, H);
+                "lstm: hidden size per direction must be a multiple of 32 in [32, %d] (got %d)", 32 * kMaxCtas, H);
     return 0;
+}
+
+size_t fwd_smem(int H, int nbe) {
+    return 2 * (size_t)NB * H * 2 + 4 * (size_t)nbe * U * 4 + 2 * (size_t)(nbe / 8) * 512 + 64 + 1024;
+}
+size_t bwd_smem(int H, int nbe) {
+    const int ncta = H / U, blk = nbe * U;
+    return (size_t)128 * (H * 2 + 16) + 2 * NB * 128 + (size_t)2 * ncta * blk * 2 + (size_t)2 * 4 * 2 * blk * 2 +
+           5 * 128 * 4 + 64 + 1024;
+}
+
+// Batch sub-tile: 8 rows per cluster when all the clusters that makes can be resident together (they
+// cannot run in waves: a cluster lives for the whole sequence), else 16.  Cached per (direction count is
+// part of the cluster count, so only the residency limit is cached).
+int pick_nbe(int B, int D, int H, bool backward) {
+    static int cached_limit[2][kMaxCtas + 1];      // [backward][ncta] -> max active clusters at NBE = 8 (+1; 0 = unknown)
+    const int ncta = H / U;
+    int& c = cached_limit[backward ? 1 : 0][ncta];
+    if (c == 0) {
+        const int n = backward ? max_active_clusters(lstm_bwd_kernel<8>, ncta, bwd_smem(H, 8))
+                               : max_active_clusters(lstm_fwd_kernel<8>, ncta, fwd_smem(H, 8));
+        c = n + 1;
+    }
+    // DNB_LSTM_NBE=8|16 forces the choice (tests exercise both instantiations; a forced 8 that does not
+    // fit would dead-lock nothing — clusters are independent — but runs in waves)
+    if (const char* e = getenv("DNB_LSTM_NBE")) {
+        if (e[0] == '8') return 8;
+        if (e[0] == '1') return 16;
+    }
+    const int tiles8 = (B + 7) / 8;
+    return (tiles8 * D <= c - 1) ? 8 : 16;
 }
 
 }  // namespace
@@ -786,9 +914,10 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
     const int ncta = d->H / U;
-    const size_t smem = 2 * (size_t)NB * d->H * 2 + 4 * NB * U * 4 + 2 * 1024 + 128 + 1024;
-    const int tiles = (d->B + NB - 1) / NB;
-    return launch_cluster(lstm_fwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
+    const int nbe = pick_nbe(d->B, d->D, d->H, false);
+    const int tiles = (d->B + nbe - 1) / nbe;
+    if (nbe == 8) return launch_cluster(lstm_fwd_kernel<8>, a, ncta * d->D * tiles, ncta, fwd_smem(d->H, 8), st);
+    return launch_cluster(lstm_fwd_kernel<16>, a, ncta * d->D * tiles, ncta, fwd_smem(d->H, 16), st);
 }
 
 DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
@@ -806,10 +935,14 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
     a.accumulate = d->accumulate;
     a.dbg = d->dbg;
     a.B = d->B; a.S = d->S; a.H = d->H; a.D = d->D;
-    for (int i = 0; i < d->D; ++i) DNB_REQUIRE(a.Whh[i] && a.db_a[i], "lstm bwd: W_hh/db[%d] missing", i);
+    for (int i = 0; i < d->D; ++i) {
+        DNB_REQUIRE(a.Whh[i] && a.db_a[i], "lstm bwd: W_hh/db[%d] missing", i);
+        DNB_REQUIRE(a.WhhT[i] == nullptr || ((uintptr_t)a.WhhT[i] & 15) == 0, "lstm bwd: W_hh^T[%d] not 16B aligned", i);
+    }
     DNB_REQUIRE(a.P && a.C && a.dHmean && a.dP, "lstm bwd: null buffer");
     const int ncta = d->H / U;
-    const int tiles = (d->B + NB - 1) / NB;
+    const int nbe = pick_nbe(d->B, d->D, d->H, true);
+    const int tiles = (d->B + nbe - 1) / nbe;
     if (tiles > 1 && !d->accumulate) {
         // several batch tiles add into the same bias-gradient vectors
         for (int i = 0; i < d->D; ++i) {
@@ -817,6 +950,6 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
             if (a.db_b[i]) DNB_CUDA_CHECK(cudaMemsetAsync(a.db_b[i], 0, sizeof(float) * 4 * d->H, st));
         }
     }
-    const size_t smem = (size_t)128 * (d->H * 2 + 16) + 2 * NB * 128 + (size_t)2 * ncta * U * NB * 4 + 128 * 4 + (size_t)2 * 4 * 2 * U * NB * 4 + 128 + 1024;
-    return launch_cluster(lstm_bwd_kernel, a, ncta * d->D * tiles, ncta, smem, st);
+    if (nbe == 8) return launch_cluster(lstm_bwd_kernel<8>, a, ncta * d->D * tiles, ncta, bwd_smem(d->H, 8), st);
+    return launch_cluster(lstm_bwd_kernel<16>, a, ncta * d->D * tiles, ncta, bwd_smem(d->H, 16), st);
 }
