@@ -86,31 +86,36 @@ struct BwdArgs {
 // per-thread roles of the cell update for a batch sub-tile of NBE rows: every thread owns UPT consecutive
 // hidden units of one batch row (NBE x 32 units over 128 threads)
 template <int NBE> struct Roles {
-    static constexpr int UPT = NBE / 4;          // units per thread: 4 (NBE 16) or 2 (NBE 8)
-    static constexpr int TPR = U / UPT;          // threads per batch row: 8 or 16
+    static constexpr int UPT = NBE / 4;          // units per thread: 4 (NBE 16), 2 (NBE 8) or 1 (NBE 4)
+    static constexpr int TPR = U / UPT;          // threads per batch row: 8, 16 or 32
 };
 
-// small fixed-size vector moves (N = 2 or 4)
+// small fixed-size vector moves (N = 1, 2 or 4)
 template <int N> __device__ __forceinline__ void ldv(float (&d)[N], const float* p) {
     if constexpr (N == 4) {
         const float4 v = *reinterpret_cast<const float4*>(p);
         d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-    } else {
+    } else if constexpr (N == 2) {
         const float2 v = *reinterpret_cast<const float2*>(p);
         d[0] = v.x; d[1] = v.y;
+    } else {
+        d[0] = *p;
     }
 }
 template <int N> __device__ __forceinline__ void stv(float* p, const float (&s)[N]) {
     if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(s[0], s[1], s[2], s[3]);
-    else *reinterpret_cast<float2*>(p) = make_float2(s[0], s[1]);
+    else if constexpr (N == 2) *reinterpret_cast<float2*>(p) = make_float2(s[0], s[1]);
+    else *p = s[0];
 }
-template <int N> struct BfPack;     // N bf16 values as one 4- or 8-byte word
+template <int N> struct BfPack;     // N bf16 values as one 2-, 4- or 8-byte word
 template <> struct BfPack<4> { uint2 w; };
 template <> struct BfPack<2> { uint32_t w; };
+template <> struct BfPack<1> { uint16_t w; };
 template <int N> __device__ __forceinline__ BfPack<N> pack_bf(const float (&s)[N]) {
     BfPack<N> r;
     if constexpr (N == 4) { r.w.x = dnb::pack_bf16x2(s[0], s[1]); r.w.y = dnb::pack_bf16x2(s[2], s[3]); }
-    else r.w = dnb::pack_bf16x2(s[0], s[1]);
+    else if constexpr (N == 2) r.w = dnb::pack_bf16x2(s[0], s[1]);
+    else r.w = __bfloat16_as_ushort(__float2bfloat16_rn(s[0]));
     return r;
 }
 template <int N> __device__ __forceinline__ BfPack<N> zero_bf() {
@@ -119,10 +124,32 @@ template <int N> __device__ __forceinline__ BfPack<N> zero_bf() {
     return r;
 }
 template <int N> __device__ __forceinline__ void st_bf(void* p, const BfPack<N>& v) {
-    if constexpr (N == 4) *reinterpret_cast<uint2*>(p) = v.w; else *reinterpret_cast<uint32_t*>(p) = v.w;
+    if constexpr (N == 4) *reinterpret_cast<uint2*>(p) = v.w;
+    else if constexpr (N == 2) *reinterpret_cast<uint32_t*>(p) = v.w;
+    else *reinterpret_cast<uint16_t*>(p) = v.w;
+}
+template <int N> __device__ __forceinline__ BfPack<N> ld_bf(const void* p) {
+    BfPack<N> r;
+    if constexpr (N == 4) r.w = *reinterpret_cast<const uint2*>(p);
+    else if constexpr (N == 2) r.w = *reinterpret_cast<const uint32_t*>(p);
+    else r.w = *reinterpret_cast<const uint16_t*>(p);
+    return r;
+}
+// d[j] += float(v[j])
+template <int N> __device__ __forceinline__ void add_bf(float (&d)[N], const BfPack<N>& v) {
+    if constexpr (N == 4) {
+        d[0] += __uint_as_float(v.w.x << 16); d[1] += __uint_as_float(v.w.x & 0xFFFF0000u);
+        d[2] += __uint_as_float(v.w.y << 16); d[3] += __uint_as_float(v.w.y & 0xFFFF0000u);
+    } else if constexpr (N == 2) {
+        d[0] += __uint_as_float(v.w << 16); d[1] += __uint_as_float(v.w & 0xFFFF0000u);
+    } else {
+        d[0] += __uint_as_float((uint32_t)v.w << 16);
+    }
 }
 template <int N> __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&v)[N]) {
-    if constexpr (N == 16) dnb::tmem_ld_32x16(taddr, v); else dnb::tmem_ld_32x8(taddr, v);
+    if constexpr (N == 16) dnb::tmem_ld_32x16(taddr, v);
+    else if constexpr (N == 8) dnb::tmem_ld_32x8(taddr, v);
+    else dnb::tmem_ld_32x4(taddr, v);
 }
 
 // byte offset of element (row, k) inside a K-major SWIZZLE_128B operand made of 64-wide k-blocks
@@ -165,7 +192,7 @@ __device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(
 // ------------------------------------------------------------------------------------ forward
 template <int NBE>
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
-    constexpr int UPT = Roles<NBE>::UPT, TPR = Roles<NBE>::TPR, NG = NBE / 8;   // NG = 8-row groups exchanged
+    constexpr int UPT = Roles<NBE>::UPT, TPR = Roles<NBE>::TPR, NG = (NBE + 7) / 8;   // NG = 8-row groups exchanged
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
     const int H = a.H;
@@ -192,11 +219,13 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     const int dir = cid % a.D, b0 = (cid / a.D) * NBE;
     const size_t ldp = (size_t)a.D * 4 * H, ldh = (size_t)a.D * H;
     const int nvalid = min(NBE, a.B - b0);           // real batch rows in this tile
-    const uint32_t h_tx_bytes = (uint32_t)(NBE * H * 2);
+    const uint32_t h_tx_bytes = (uint32_t)(NG * 8 * H * 2);   // whole 8-row groups travel (rows >= NBE are zeros)
 
     // ---- one-time: zero h_{-1}; the weight slice goes to tensor memory once the allocation exists
     for (int idx = tid; idx < 2 * h_bytes / 16; idx += kThreads)
         reinterpret_cast<uint4*>(sH)[idx] = make_uint4(0, 0, 0, 0);
+    for (int idx = tid; idx < 2 * NG * 512 / 16; idx += kThreads)
+        reinterpret_cast<uint4*>(sStage)[idx] = make_uint4(0, 0, 0, 0);
     if (warp == 0) {
         if (lane == 0) {
             dnb::mbar_init(mma_bar, 1);
@@ -720,21 +749,10 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
             const __nv_bfloat16* red_par = sRed + (size_t)(n & 1) * ncta * BLK + b2 * U + u0;
             BfPack<UPT> part[kMaxCtas];
 #pragma unroll
-            for (int src = 0; src < kMaxCtas; ++src) {     // constant offsets; all loads issued before the adds
-                if (src < ncta) {
-                    if constexpr (UPT == 4) part[src].w = *reinterpret_cast<const uint2*>(red_par + src * BLK);
-                    else part[src].w = *reinterpret_cast<const uint32_t*>(red_par + src * BLK);
-                } else part[src] = zero_bf<UPT>();
-            }
+            for (int src = 0; src < kMaxCtas; ++src)       // constant offsets; all loads issued before the adds
+                part[src] = (src < ncta) ? ld_bf<UPT>(red_par + src * BLK) : zero_bf<UPT>();
 #pragma unroll
-            for (int src = 0; src < kMaxCtas; ++src) {
-                if constexpr (UPT == 4) {
-                    dh[0] += __uint_as_float(part[src].w.x << 16); dh[1] += __uint_as_float(part[src].w.x & 0xFFFF0000u);
-                    dh[2] += __uint_as_float(part[src].w.y << 16); dh[3] += __uint_as_float(part[src].w.y & 0xFFFF0000u);
-                } else {
-                    dh[0] += __uint_as_float(part[src].w << 16); dh[1] += __uint_as_float(part[src].w & 0xFFFF0000u);
-                }
-            }
+            for (int src = 0; src < kMaxCtas; ++src) add_bf<UPT>(dh, part[src]);
         }
         DNB_STAMP(8);
         float dp[4][UPT];
@@ -865,7 +883,7 @@ int check_shape(int B, int S, int H, int D) {
 }
 
 size_t fwd_smem(int H, int nbe) {
-    return 2 * (size_t)NB * H * 2 + 4 * (size_t)nbe * U * 4 + 2 * (size_t)(nbe / 8) * 512 + 64 + 1024;
+    return 2 * (size_t)NB * H * 2 + 4 * (size_t)nbe * U * 4 + 2 * (size_t)((nbe + 7) / 8) * 512 + 64 + 1024;
 }
 size_t bwd_smem(int H, int nbe) {
     const int ncta = H / U, blk = nbe * U;
@@ -877,22 +895,33 @@ size_t bwd_smem(int H, int nbe) {
 // cannot run in waves: a cluster lives for the whole sequence), else 16.  Cached per (direction count is
 // part of the cluster count, so only the residency limit is cached).
 int pick_nbe(int B, int D, int H, bool backward) {
-    static int cached_limit[2][kMaxCtas + 1];      // [backward][ncta] -> max active clusters at NBE = 8 (+1; 0 = unknown)
+    static int cached_limit[2][kMaxCtas + 1];      // [backward][ncta] -> max active clusters (+1; 0 = unknown)
     const int ncta = H / U;
     int& c = cached_limit[backward ? 1 : 0][ncta];
     if (c == 0) {
+        // the NBE = 8 instantiation has the larger footprint of the two small ones
         const int n = backward ? max_active_clusters(lstm_bwd_kernel<8>, ncta, bwd_smem(H, 8))
                                : max_active_clusters(lstm_fwd_kernel<8>, ncta, fwd_smem(H, 8));
         c = n + 1;
     }
-    // DNB_LSTM_NBE=8|16 forces the choice (tests exercise both instantiations; a forced 8 that does not
-    // fit would dead-lock nothing — clusters are independent — but runs in waves)
+    // DNB_LSTM_NBE=4|8|16 forces the choice (tests exercise every instantiation; a forced value that does
+    // not fit dead-locks nothing — clusters are independent — but runs in waves)
     if (const char* e = getenv("DNB_LSTM_NBE")) {
+        if (e[0] == '4') return 4;
         if (e[0] == '8') return 8;
         if (e[0] == '1') return 16;
     }
-    const int tiles8 = (B + 7) / 8;
-    return (tiles8 * D <= c - 1) ? 8 : 16;
+    if (((B + 3) / 4) * D <= c - 1) return 4;
+    if (((B + 7) / 8) * D <= c - 1) return 8;
+    return 16;
+}
+
+template <typename Args>
+int launch_nbe(int nbe, void (*k4)(const Args), void (*k8)(const Args), void (*k16)(const Args), const Args& a, int B, int D,
+               int ncta, size_t (*smem_of)(int, int), int H, cudaStream_t st) {
+    const int tiles = (B + nbe - 1) / nbe;
+    void (*k)(const Args) = nbe == 4 ? k4 : (nbe == 8 ? k8 : k16);
+    return launch_cluster(k, a, ncta * D * tiles, ncta, smem_of(H, nbe), st);
 }
 
 }  // namespace
@@ -913,11 +942,8 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
     for (int i = 0; i < d->D; ++i)
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
-    const int ncta = d->H / U;
-    const int nbe = pick_nbe(d->B, d->D, d->H, false);
-    const int tiles = (d->B + nbe - 1) / nbe;
-    if (nbe == 8) return launch_cluster(lstm_fwd_kernel<8>, a, ncta * d->D * tiles, ncta, fwd_smem(d->H, 8), st);
-    return launch_cluster(lstm_fwd_kernel<16>, a, ncta * d->D * tiles, ncta, fwd_smem(d->H, 16), st);
+    return launch_nbe(pick_nbe(d->B, d->D, d->H, false), lstm_fwd_kernel<4>, lstm_fwd_kernel<8>, lstm_fwd_kernel<16>, a,
+                      d->B, d->D, d->H / U, fwd_smem, d->H, st);
 }
 
 DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
@@ -950,6 +976,5 @@ DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
             if (a.db_b[i]) DNB_CUDA_CHECK(cudaMemsetAsync(a.db_b[i], 0, sizeof(float) * 4 * d->H, st));
         }
     }
-    if (nbe == 8) return launch_cluster(lstm_bwd_kernel<8>, a, ncta * d->D * tiles, ncta, bwd_smem(d->H, 8), st);
-    return launch_cluster(lstm_bwd_kernel<16>, a, ncta * d->D * tiles, ncta, bwd_smem(d->H, 16), st);
+    return launch_nbe(nbe, lstm_bwd_kernel<4>, lstm_bwd_kernel<8>, lstm_bwd_kernel<16>, a, d->B, d->D, ncta, bwd_smem, d->H, st);
 }

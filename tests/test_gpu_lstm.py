@@ -24,7 +24,7 @@ def _px(lstm, enc, B, S, H, D):
     return px
 
 
-@pytest.mark.parametrize("nbe", ["auto", "8", "16"])      # batch sub-tile per cluster (csrc/lstm.cu pick_nbe)
+@pytest.mark.parametrize("nbe", ["auto", "4", "8", "16"])      # batch sub-tile per cluster (csrc/lstm.cu pick_nbe)
 @pytest.mark.parametrize("B,S,H,D", [(16, 98, 192, 2), (5, 7, 32, 1), (16, 12, 64, 2), (40, 9, 96, 2), (3, 20, 256, 2)])
 def test_lstm_forward_and_backward(B, S, H, D, nbe, monkeypatch):
     from dinunet_implementations_b200.ops.lstm import lstm_forward, lstm_backward
