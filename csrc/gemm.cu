@@ -54,14 +54,15 @@ struct SmemLayout {
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Epi epi,
-                 int M, int N, int K, int k_tiles_per_split) {
+                 int M, int N, int K, int k_tiles_per_split, int STAGES) {
     using L = SmemLayout<BN>;
-    constexpr int STAGES = L::kStages;
     constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (dnb::smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+    // STAGES (<= L::kStages) is chosen by the host: a short K loop does not need the full ring, and a
+    // smaller footprint lets two CTAs share an SM when the tile count slightly exceeds one wave
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * L::kStageBytes);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
@@ -288,7 +289,23 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Epi& e, int M, in
     int per = (total_kt + splits - 1) / splits;
     int real_splits = (total_kt + per - 1) / per;
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, real_splits);
-    gemm_bf16_kernel<BN><<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, e, M, N, K, per);
+    int stages = per < L::kStages ? per : L::kStages;
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const long ctas = (long)grid.x * grid.y * grid.z;
+    if (ctas > sms && ctas <= 2L * sms && BN <= 128) {
+        // a bit more than one wave: shrink the ring so that two CTAs fit on an SM (<= ~110 KB each, TMEM
+        // 2 x BN columns) and the whole grid is resident at once instead of running a nearly empty second wave
+        const int fit = (108 * 1024) / L::kStageBytes;
+        if (fit >= 2 && stages > fit) stages = fit;
+    }
+    if (stages < 1) stages = 1;
+    const size_t smem = (size_t)stages * L::kStageBytes + (2 * L::kStages + 1) * 8 + 16 + 1024;
+    gemm_bf16_kernel<BN><<<grid, kGemmThreads, smem, st>>>(ta, tb, e, M, N, K, per, stages);
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;
