@@ -33,6 +33,8 @@ struct HeadFwdArgs {
     float momentum, eps; int training;
     float *a0, *xhat, *invstd, *a1, *a2, *logits;
     int B, N0, N1, N2, N3;
+    float* drop_out; float drop_p; unsigned long long drop_seed; unsigned long long* drop_state;
+    long long* nbt;
 };
 
 struct HeadBwdArgs {
@@ -59,6 +61,15 @@ __device__ __forceinline__ float sum16(float v) {
     return v;
 }
 
+// Counter-based dropout: 64 random bits per group of 4 elements from splitmix64(seed, step, group index);
+// element e keeps its value (scaled by 1/(1-p)) when its 16-bit lane is >= p * 65536.
+__device__ __forceinline__ uint64_t drop_bits(uint64_t seed, uint64_t step, uint32_t group) {
+    uint64_t z = seed + step * 0xD1B54A32D192ED03ull + (uint64_t)group * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
 __device__ __forceinline__ float dot8(const uint4& w, const float4& x0, const float4& x1) {
     return __uint_as_float(w.x << 16) * x0.x + __uint_as_float(w.x & 0xFFFF0000u) * x0.y +
            __uint_as_float(w.y << 16) * x0.z + __uint_as_float(w.y & 0xFFFF0000u) * x0.w +
@@ -79,12 +90,25 @@ __global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a
         const int per_row = N0 / 4;
         const float4* x4 = reinterpret_cast<const float4*>(a.x);
         const float4* d4 = reinterpret_cast<const float4*>(a.drop);
+        const bool gen = d4 == nullptr && a.drop_state != nullptr && a.drop_p > 0.f;
+        const uint64_t step = gen ? *a.drop_state : 0ull;       // advanced by launch 2 (after every CTA has read it)
+        const uint32_t thr = gen ? (uint32_t)(a.drop_p * 65536.f) : 0u;
+        const float keep = gen ? 1.f / (1.f - a.drop_p) : 1.f;
 #pragma unroll 4
         for (int i = tid; i < B * per_row; i += kF1Threads) {
             float4 v = x4[i];
             if (d4) {
                 const float4 d = d4[i];
                 v.x *= d.x; v.y *= d.y; v.z *= d.z; v.w *= d.w;
+            } else if (gen) {
+                const uint64_t r = drop_bits(a.drop_seed, step, (uint32_t)i);
+                float4 d;
+                d.x = ((uint32_t)(r & 0xFFFF) >= thr) ? keep : 0.f;
+                d.y = ((uint32_t)((r >> 16) & 0xFFFF) >= thr) ? keep : 0.f;
+                d.z = ((uint32_t)((r >> 32) & 0xFFFF) >= thr) ? keep : 0.f;
+                d.w = ((uint32_t)(r >> 48) >= thr) ? keep : 0.f;
+                v.x *= d.x; v.y *= d.y; v.z *= d.z; v.w *= d.w;
+                if (blockIdx.x == 0) reinterpret_cast<float4*>(a.drop_out)[i] = d;
             }
             const int r = i / per_row, c = i % per_row;
             *reinterpret_cast<float4*>(xs + r * ldx + c * 4) = v;
@@ -187,6 +211,10 @@ __global__ void __launch_bounds__(kF2Threads) head_f2_kernel(const HeadFwdArgs a
         }
     }
     __syncthreads();
+    if (blockIdx.x == 0 && tid == 0) {     // bookkeeping that must follow launch 1 as a whole
+        if (a.drop == nullptr && a.drop_state != nullptr && a.drop_p > 0.f) *a.drop_state += 1ull;
+        if (a.nbt != nullptr && a.training) *a.nbt += 1ll;
+    }
     const int nf = min(kF2Feat, N2 - j0);
     for (int idx = tid; idx < B * N3; idx += kF2Threads) {
         const int b = idx / N3, c = idx % N3;
@@ -404,6 +432,12 @@ DNB_EXPORT int dnb_head_forward(const DnbHeadFwdDesc* d, void* stream_) {
     a.run_mean = d->run_mean; a.run_var = d->run_var; a.momentum = d->momentum; a.eps = d->eps; a.training = d->training;
     a.a0 = d->a0; a.xhat = d->xhat; a.invstd = d->invstd; a.a1 = d->a1; a.a2 = d->a2; a.logits = d->logits;
     a.B = d->B; a.N0 = d->N0; a.N1 = d->N1; a.N2 = d->N2; a.N3 = d->N3;
+    a.drop_out = d->drop_out; a.drop_p = d->drop_p; a.drop_seed = d->drop_seed; a.drop_state = d->drop_state;
+    a.nbt = d->num_batches_tracked;
+    if (a.drop == nullptr && a.drop_state != nullptr && a.drop_p > 0.f) {
+        DNB_REQUIRE(a.drop_p < 1.f && a.drop_out != nullptr && a.a0 != nullptr,
+                    "head fwd: in-kernel dropout needs 0 < p < 1 and the drop_out / a0 buffers");
+    }
     DNB_REQUIRE(a.x && a.W1 && a.W2 && a.W3 && a.xhat && a.invstd && a.a1 && a.a2 && a.logits, "head fwd: null buffer");
     DNB_REQUIRE(a.training || (a.run_mean && a.run_var), "head fwd: eval mode needs running statistics");
     {

@@ -78,11 +78,14 @@ class _SoftmaxCE(torch.autograd.Function):
                      "dnb_softmax_ce")
         ctx.save_for_backward(dlogits)
         ctx.mark_non_differentiable(prob)
+        ctx.set_materialize_grads(False)       # no zero tensor for the gradient of prob
         return loss, prob
 
     @staticmethod
     def backward(ctx, gloss, gprob):
         (dlogits,) = ctx.saved_tensors
+        if gloss is None:
+            return None, None, None
         return dlogits * gloss, None, None
 
 

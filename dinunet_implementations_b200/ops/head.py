@@ -8,12 +8,20 @@ import torch
 from . import native
 
 
-def head_forward(x, drop, W1, b1, bn_w, bn_b, run_mean, run_var, W2, b2, W3, b3, training, momentum=0.1, eps=1e-5):
-    """Returns ``(logits, saved)``; ``saved`` feeds ``head_backward``.  Weights bf16, rest fp32."""
+def head_forward(x, drop, W1, b1, bn_w, bn_b, run_mean, run_var, W2, b2, W3, b3, training, momentum=0.1, eps=1e-5,
+                 gen_drop=None, num_batches_tracked=None):
+    """Returns ``(logits, saved)``; ``saved`` feeds ``head_backward``.  Weights bf16, rest fp32.
+
+    Dropout: either pass the scale mask ``drop`` ``[B,N0]``, or ``gen_drop=(p, seed, state)`` with ``state`` a
+    device int64 scalar — the kernel then draws the mask itself (no RNG launches) and advances ``state``.
+    ``num_batches_tracked`` (device int64 scalar) is incremented by the kernel in training mode."""
     lib = native.require_gpu()
     B, N0 = x.shape
     N1, N2, N3 = W1.shape[0], W2.shape[0], W3.shape[0]
     dev = x.device
+    gen = drop is None and gen_drop is not None and float(gen_drop[0]) > 0
+    if gen:
+        drop = torch.empty(B, N0, device=dev)          # written by the kernel
     a0 = torch.empty(B, N0, device=dev) if drop is not None else None
     xhat = torch.empty(B, N1, device=dev)
     invstd = torch.empty(N1, device=dev)
@@ -21,7 +29,14 @@ def head_forward(x, drop, W1, b1, bn_w, bn_b, run_mean, run_var, W2, b2, W3, b3,
     a2 = torch.empty(B, N2, device=dev)
     logits = torch.empty(B, N3, device=dev)
     d = native.HeadFwdDesc()
-    d.x, d.drop = x.data_ptr(), (drop.data_ptr() if drop is not None else None)
+    d.x, d.drop = x.data_ptr(), (drop.data_ptr() if (drop is not None and not gen) else None)
+    if gen:
+        p_, seed_, state_ = gen_drop
+        assert state_.dtype == torch.int64 and state_.is_cuda
+        d.drop_out, d.drop_p, d.drop_seed, d.drop_state = drop.data_ptr(), float(p_), int(seed_) & (2 ** 64 - 1), state_.data_ptr()
+    if num_batches_tracked is not None:
+        assert num_batches_tracked.dtype == torch.int64 and num_batches_tracked.is_cuda
+        d.num_batches_tracked = num_batches_tracked.data_ptr()
     d.W1, d.W2, d.W3 = W1.data_ptr(), W2.data_ptr(), W3.data_ptr()
     d.b1, d.b2, d.b3 = b1.data_ptr(), b2.data_ptr(), b3.data_ptr()
     d.bn_w, d.bn_b = bn_w.data_ptr(), bn_b.data_ptr()

@@ -224,19 +224,25 @@ class _ICALstmFn(torch.autograd.Function):
             hT, cT = pad.unpad(hT), pad.unpad(cT)
         # 5. head
         N0 = D * H
-        drop = None
         p_drop = cls[0].p
+        gen_drop = None
         if training and p_drop > 0:
-            drop = torch.empty(B, N0, device=x.device, dtype=torch.float32).bernoulli_(1 - p_drop).div_(1 - p_drop)
+            # the head kernel draws the dropout mask itself from (seed, device-resident step counter): no RNG
+            # launches, and the captured step replays with a fresh mask every time
+            st = model.__dict__.setdefault("_drop_state", {})
+            key = (x.device.type, x.device.index)
+            if key not in st:
+                st[key] = (torch.zeros((), device=x.device, dtype=torch.int64), torch.initial_seed())
+            gen_drop = (float(p_drop), st[key][1], st[key][0])
         W1 = _w16(model, cls[1].weight) if pad is None else pad.W1
         W2, W3 = _w16(model, cls[4].weight), _w16(model, cls[6].weight)
         bn = cls[2]
-        logits, head_saved = head_forward(Hmean, drop, W1, cls[1].bias.detach(), bn.weight.detach(), bn.bias.detach(),
+        logits, head_saved = head_forward(Hmean, None, W1, cls[1].bias.detach(), bn.weight.detach(), bn.bias.detach(),
                                           bn.running_mean, bn.running_var, W2, cls[4].bias.detach(), W3,
-                                          cls[6].bias.detach(), training, float(bn.momentum or 0.1), float(bn.eps))
-        if training:
-            bn.num_batches_tracked += 1
+                                          cls[6].bias.detach(), training, float(bn.momentum or 0.1), float(bn.eps),
+                                          gen_drop=gen_drop, num_batches_tracked=bn.num_batches_tracked if training else None)
 
+        ctx.set_materialize_grads(False)       # no zero tensors for the (unused) gradients of hT / cT
         ctx.model = model
         ctx.dims = (B, S, E, H, D)
         ctx.pad = pad
@@ -248,6 +254,8 @@ class _ICALstmFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dlogits, _dh, _dc):
         lib = native.require_gpu()
+        if dlogits is None:      # only the (non-differentiable) final states were used downstream
+            return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
         model = ctx.model
         B, S, E, H, D = ctx.dims
         (xT, enc, encT, P, C, Hprev, whh, w_ih, head_saved) = ctx.saved

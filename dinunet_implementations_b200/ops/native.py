@@ -211,6 +211,8 @@ class HeadFwdDesc(ctypes.Structure):
         ("xhat", ctypes.c_void_p), ("invstd", ctypes.c_void_p), ("a1", ctypes.c_void_p), ("a2", ctypes.c_void_p),
         ("logits", ctypes.c_void_p),
         ("B", ctypes.c_int), ("N0", ctypes.c_int), ("N1", ctypes.c_int), ("N2", ctypes.c_int), ("N3", ctypes.c_int),
+        ("drop_out", ctypes.c_void_p), ("drop_p", ctypes.c_float), ("drop_seed", ctypes.c_ulonglong),
+        ("drop_state", ctypes.c_void_p), ("num_batches_tracked", ctypes.c_void_p),
     ]
 
 

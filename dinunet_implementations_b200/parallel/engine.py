@@ -120,6 +120,7 @@ class DeviceEngine:
                     for sub in m.modules():
                         sub._bf16_shadow = shadow
         self.steps = 0
+        self._one = None
         self.timer = None
         if self.cache.get("profile_enabled"):
             from ..utils.profiler import PhaseTimer
@@ -160,7 +161,10 @@ class DeviceEngine:
         with self._ph("forward"):
             it = self.trainer.iteration(batch)
         with self._ph("backward"):
-            it["loss"].backward()
+            loss = it["loss"]
+            if self._one is None or self._one.dtype != loss.dtype or self._one.shape != loss.shape:
+                self._one = torch.ones_like(loss)          # persistent seed gradient: no fill launch per step
+            loss.backward(gradient=self._one)
         with self._ph("aggregate+update"):
             self.fused.step()
         if self.train_metrics is not None and it.get("out") is not None and "labels" in batch:

@@ -174,6 +174,15 @@ typedef struct DnbHeadFwdDesc {
     float* a0;                 /* [B,N0] dropped input (NULL: not saved) */
     float *xhat, *invstd, *a1, *a2, *logits;   /* [B,N1], [N1], [B,N1], [B,N2], [B,N3] */
     int B, N0, N1, N2, N3;
+    /* optional, all may be 0/NULL.  In-kernel dropout: when drop == NULL, drop_p > 0 and drop_state != NULL the
+     * kernel draws the mask itself (counter-based hash of drop_seed, *drop_state and the element index), writes
+     * the scale values (0 or 1/(1-p)) to drop_out [B,N0] for the backward pass and advances *drop_state by one.
+     * num_batches_tracked (int64 scalar) is incremented in training mode (BatchNorm1d bookkeeping). */
+    float* drop_out;
+    float drop_p;
+    unsigned long long drop_seed;
+    unsigned long long* drop_state;
+    long long* num_batches_tracked;
 } DnbHeadFwdDesc;
 int dnb_head_forward(const DnbHeadFwdDesc* desc, void* stream);
 

@@ -59,3 +59,43 @@ def test_head_forward_backward(B, training, use_drop):
     head_backward(G, saved, grads, accumulate=True)
     torch.cuda.synchronize()
     assert torch.allclose(grads["dW3"], 2 * head[5].weight.grad, atol=4e-3 * max(head[5].weight.grad.abs().max().item(), 1e-3))
+
+
+def test_head_in_kernel_dropout_and_batch_counter():
+    """gen_drop: the kernel draws the mask (no RNG launches), hands it to the backward, advances the counter."""
+    from dinunet_implementations_b200.ops.head import head_forward, head_backward
+    B, N0, N1, N2, N3 = 32, 384, 256, 64, 2
+    head = _mods(N0, N1, N2, N3)
+    head.train(True)
+    x = torch.randn(B, N0, device="cuda", requires_grad=True)
+    state = torch.zeros((), device="cuda", dtype=torch.int64)
+    nbt = torch.zeros((), device="cuda", dtype=torch.int64)
+    args = (head[0].weight.detach().to(torch.bfloat16), head[0].bias.detach(), head[1].weight.detach(), head[1].bias.detach(),
+            head[1].running_mean.clone(), head[1].running_var.clone(), head[3].weight.detach().to(torch.bfloat16),
+            head[3].bias.detach(), head[5].weight.detach().to(torch.bfloat16), head[5].bias.detach(), True)
+    masks = []
+    for step in range(3):
+        logits, saved = head_forward(x.detach(), None, *args, gen_drop=(0.25, 1234, state), num_batches_tracked=nbt)
+        torch.cuda.synchronize()
+        m = saved["drop"]
+        assert all(v == 0.0 or abs(v - 1.0 / 0.75) < 1e-6 for v in torch.unique(m).tolist())
+        keep = (m > 0).float().mean().item()
+        assert abs(keep - 0.75) < 0.03, keep
+        assert torch.equal(saved["a0"], x.detach() * m)
+        assert int(state) == step + 1 and int(nbt) == step + 1
+        masks.append(m.clone())
+    assert not torch.equal(masks[0], masks[1]) and not torch.equal(masks[1], masks[2])
+    # same (seed, step) -> same mask; the emitted mask reproduces the torch result
+    state2 = torch.zeros((), device="cuda", dtype=torch.int64)
+    _, saved2 = head_forward(x.detach(), None, *args, gen_drop=(0.25, 1234, state2))
+    assert torch.equal(saved2["drop"], masks[0])
+    ref = head(x * m)
+    assert torch.allclose(logits, ref, atol=2e-4, rtol=1e-4)
+    G = torch.randn(B, N3, device="cuda")
+    (ref * G).sum().backward()
+    grads = {k: torch.zeros_like(p) for k, p in dict(dW1=head[0].weight, db1=head[0].bias, dbn_w=head[1].weight,
+                                                     dbn_b=head[1].bias, dW2=head[3].weight, db2=head[3].bias,
+                                                     dW3=head[5].weight, db3=head[5].bias).items()}
+    dx = head_backward(G, saved, grads, accumulate=True)
+    s = max(x.grad.abs().max().item(), 1e-3)
+    assert torch.allclose(dx, x.grad, atol=2e-3 * s)
