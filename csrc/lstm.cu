@@ -189,8 +189,26 @@ __device__ __forceinline__ constexpr uint64_t koff_b(int k) { return (uint64_t)(
 // forward B operand (h_{t-1}) is stored without swizzle: one K=16 step = two 128-byte core matrices
 __device__ __forceinline__ constexpr uint64_t koff_h(int k) { return (uint64_t)(k * (256 / 16)); }
 
+// One recurrent GEMM = KS tcgen05.mma of K = 16.  KS is a template parameter (dispatched by a switch on
+// H/16): with a run-time bound every instruction of the unrolled loop is predicated and gets its own
+// descriptor / instruction-descriptor register pairs set up on the uniform datapath — ~10 uniform
+// instructions per MMA, serial, 300 cycles per step before the first MMA result could even be waited for
+// (and a switch inside the kernel costs an indirect branch per step, which is worse).
+// Hence KS is a template parameter of the kernel for the common sizes (KS = 0: run-time bound).
+template <int KS>
+__device__ __forceinline__ void issue_recurrent_mma(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, int ksteps) {
+    if constexpr (KS > 0) {
+#pragma unroll
+        for (int k = 0; k < KS; ++k) dnb::umma_bf16_ts(tmem_d, tmem_a + k * 8, db + koff_h(k), idesc, k != 0);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            if (k < ksteps) dnb::umma_bf16_ts(tmem_d, tmem_a + k * 8, db + koff_h(k), idesc, k != 0);
+    }
+}
+
 // ------------------------------------------------------------------------------------ forward
-template <int NBE>
+template <int NBE, int KS>
 __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) {
     constexpr int UPT = Roles<NBE>::UPT, TPR = Roles<NBE>::TPR, NG = (NBE + 7) / 8;   // NG = 8-row groups exchanged
     extern __shared__ uint8_t smem_raw[];
@@ -250,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     // A operand: lane = gate row (the same row this thread owns in the epilogue), 32-bit column j =
     // k-elements 2j, 2j+1
     {
-        const uint4* wrow = reinterpret_cast<const uint4*>(a.Whh[dir] + (size_t)grow * H);
+        const uint4* wrow = reinterpret_cast<const uint4*>((dir ? a.Whh[1] : a.Whh[0]) + (size_t)grow * H);
         const uint32_t a_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + kTmemA;
         for (int c0 = 0; c0 < H / 16; c0 += 4) {
             uint4 v[8];
@@ -270,7 +288,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     dnb::tc_fence_before();
     dnb::cluster_sync_all();       // every CTA's buffers and barriers exist before anyone writes remotely
     dnb::tc_fence_after();
-    const float bias = a.bhh[dir][grow];
+    const float bias = (dir ? a.bhh[1] : a.bhh[0])[grow];   // (no dynamic indexing of kernel arguments: it copies them to local memory)
     // epilogue-2 role: thread = (batch row b2, UPT consecutive units from u0)
     const int b2 = tid / TPR, u0 = (tid % TPR) * UPT;
     const bool b2_ok = b2 < nvalid;
@@ -351,10 +369,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
             const uint64_t db_base = (t & 1) ? db_base1 : db_base0;
             if (dnb::elect_one()) {
                 if (t > 0 && t + 2 < a.S) dnb::mbar_expect_tx(&hbar[t & 1], h_tx_bytes);   // arm for step t+2
-#pragma unroll
-                for (int k = 0; k < 16; ++k)
-                    if (k < ksteps)
-                        dnb::umma_bf16_ts(tmem_u, tmem_u + kTmemA + k * 8, db_base + koff_h(k), idesc, k != 0);
+                issue_recurrent_mma<KS>(tmem_u, tmem_u + kTmemA, db_base, idesc, ksteps);
                 dnb::umma_commit(mma_bar);
             }
             __syncwarp();
@@ -497,8 +512,8 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     // CTA's 128 gate rows of W_hh in shared memory (row-major, coalesced 16-byte loads) for the transposition
     for (int idx = tid; idx < (2 * NB * 128) / 16; idx += kThreads)
         reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
-    const __nv_bfloat16* W = a.Whh[dir];
-    const __nv_bfloat16* WT = a.WhhT[dir];
+    const __nv_bfloat16* W = dir ? a.Whh[1] : a.Whh[0];
+    const __nv_bfloat16* WT = dir ? a.WhhT[1] : a.WhhT[0];
     if (WT == nullptr) {
         const int cpr = H / 8;                            // 16-byte chunks per row
         for (int base = 0; base < 128 * cpr; base += kThreads * 8) {
@@ -604,9 +619,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t db_base = dnb::umma_desc_k_sw128(__shfl_sync(0xffffffffu, dnb::smem_u32(sB), 0));
     // where this CTA's partial-dh blocks land in an owner's sRed: [parity][source = this CTA]
-    const uint32_t red_blk[2] = {dnb::smem_u32(sRed + (size_t)cta * BLK),
-                                 dnb::smem_u32(sRed + (size_t)ncta * BLK + (size_t)cta * BLK)};
-    const uint32_t rbar_local[2] = {dnb::smem_u32(&rbar[0]), dnb::smem_u32(&rbar[1])};
+    const uint32_t red_blk0 = dnb::smem_u32(sRed + (size_t)cta * BLK);      // + parity * red_par_bytes
+    const uint32_t red_par_bytes = (uint32_t)(ncta * BLK * 2);
+    const uint32_t rbar_u = dnb::smem_u32(&rbar[0]);                        // + parity * 8
     const uint32_t sB_off[4] = {sw128_off(NB, b2, 0 * U + u0), sw128_off(NB, b2, 1 * U + u0),
                                 sw128_off(NB, b2, 2 * U + u0), sw128_off(NB, b2, 3 * U + u0)};
 
@@ -738,9 +753,9 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt)
                     if (mt < MT && mt * 4 + warp < ncta)
-                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk[n & 1], mt * 4 + warp),
+                        dnb::bulk_copy_smem_to_cluster(dnb::mapa(red_blk0 + (n & 1) * red_par_bytes, mt * 4 + warp),
                                                        dnb::smem_u32(stg + mt * BLK), BLK * 2,
-                                                       dnb::mapa(rbar_local[n & 1], mt * 4 + warp));
+                                                       dnb::mapa(rbar_u + (n & 1) * 8, mt * 4 + warp));
             }
             DNB_STAMP(6);
             dnb::tc_fence_before();
@@ -807,13 +822,15 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     {
         const int gr = (tid >> 5) * H + cta * U + (tid & 31);
         const float v = sDb[tid] + sDb[128 + tid] + sDb[256 + tid] + sDb[384 + tid];
+        float* dba = dir ? a.db_a[1] : a.db_a[0];
+        float* dbb = dir ? a.db_b[1] : a.db_b[0];
         // batch tiles of the same direction add into the same vector
         if (a.accumulate || gridDim.x > (unsigned)(ncta * a.D)) {
-            atomicAdd(a.db_a[dir] + gr, v);
-            if (a.db_b[dir]) atomicAdd(a.db_b[dir] + gr, v);
+            atomicAdd(dba + gr, v);
+            if (dbb) atomicAdd(dbb + gr, v);
         } else {
-            a.db_a[dir][gr] = v;
-            if (a.db_b[dir]) a.db_b[dir][gr] = v;
+            dba[gr] = v;
+            if (dbb) dbb[gr] = v;
         }
     }
     dnb::tc_fence_before();
@@ -901,7 +918,7 @@ int pick_nbe(int B, int D, int H, bool backward) {
     if (c == 0) {
         // the NBE = 8 instantiation has the larger footprint of the two small ones
         const int n = backward ? max_active_clusters(lstm_bwd_kernel<8>, ncta, bwd_smem(H, 8))
-                               : max_active_clusters(lstm_fwd_kernel<8>, ncta, fwd_smem(H, 8));
+                               : max_active_clusters(lstm_fwd_kernel<8, 0>, ncta, fwd_smem(H, 8));
         c = n + 1;
     }
     // DNB_LSTM_NBE=4|8|16 forces the choice (tests exercise every instantiation; a forced value that does
@@ -942,8 +959,15 @@ DNB_EXPORT int dnb_lstm_forward(const DnbLstmFwdDesc* d, void* stream_) {
     for (int i = 0; i < d->D; ++i)
         DNB_REQUIRE(a.Whh[i] && a.bhh[i] && ((uintptr_t)a.Whh[i] & 15) == 0, "lstm fwd: W_hh[%d] missing or not 16B aligned", i);
     DNB_REQUIRE(a.PX && a.C && a.Hprev && a.Hmean, "lstm fwd: null buffer");
-    return launch_nbe(pick_nbe(d->B, d->D, d->H, false), lstm_fwd_kernel<4>, lstm_fwd_kernel<8>, lstm_fwd_kernel<16>, a,
-                      d->B, d->D, d->H / U, fwd_smem, d->H, st);
+    const int nbe = pick_nbe(d->B, d->D, d->H, false);
+    switch (d->H / 16) {      // specialised recurrent-GEMM length for the common hidden sizes
+        case 4: return launch_nbe(nbe, lstm_fwd_kernel<4, 4>, lstm_fwd_kernel<8, 4>, lstm_fwd_kernel<16, 4>, a, d->B, d->D, d->H / U, fwd_smem, d->H, st);
+        case 8: return launch_nbe(nbe, lstm_fwd_kernel<4, 8>, lstm_fwd_kernel<8, 8>, lstm_fwd_kernel<16, 8>, a, d->B, d->D, d->H / U, fwd_smem, d->H, st);
+        case 12: return launch_nbe(nbe, lstm_fwd_kernel<4, 12>, lstm_fwd_kernel<8, 12>, lstm_fwd_kernel<16, 12>, a, d->B, d->D, d->H / U, fwd_smem, d->H, st);
+        case 16: return launch_nbe(nbe, lstm_fwd_kernel<4, 16>, lstm_fwd_kernel<8, 16>, lstm_fwd_kernel<16, 16>, a, d->B, d->D, d->H / U, fwd_smem, d->H, st);
+        default: break;
+    }
+    return launch_nbe(nbe, lstm_fwd_kernel<4, 0>, lstm_fwd_kernel<8, 0>, lstm_fwd_kernel<16, 0>, a, d->B, d->D, d->H / U, fwd_smem, d->H, st);
 }
 
 DNB_EXPORT int dnb_lstm_backward(const DnbLstmBwdDesc* d, void* stream_) {
