@@ -28,6 +28,14 @@ DNB_EXPORT const char* dnb_last_error(void) { return g_err; }
 DNB_EXPORT int dnb_version(void) { return 100; }
 
 void dnb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool dnb_pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("DNB_PDL");
+        return e && e[0] == '1';      // opt-in: see common.cuh
+    }();
+    return on;
+}
 DNB_EXPORT long long dnb_launch_count(void) { return g_launches.load(); }
 DNB_EXPORT void dnb_reset_launch_count(void) { g_launches.store(0); }
 

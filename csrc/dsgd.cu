@@ -102,6 +102,7 @@ template <int WIRE>
 __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs a) {
     // Step-dependent scalars come either from the launch arguments or — when the launch lives in a
     // CUDA graph and is replayed unchanged — from a small device-resident state block.
+    dnb::pdl_wait();
     uint32_t epoch = a.epoch;
     float lr = a.lr, bc1 = a.bc1, bc2 = a.bc2;
     uint32_t t_dev = 0;
@@ -240,9 +241,9 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     if (blocks > kMaxBlocks) blocks = kMaxBlocks;
     if (blocks < 1) blocks = 1;
     switch (d->wire) {
-        case 0: dsgd_fused_kernel<0><<<blocks, kThreads, 0, stream>>>(a); break;
-        case 1: dsgd_fused_kernel<1><<<blocks, kThreads, 0, stream>>>(a); break;
-        default: dsgd_fused_kernel<2><<<blocks, kThreads, 0, stream>>>(a); break;
+        case 0: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<0>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
+        case 1: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<1>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
+        default: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<2>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
     }
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);

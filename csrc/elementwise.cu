@@ -12,6 +12,8 @@ namespace {
 __global__ void cast_time_major_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ rows, long long ldr,
                                        __nv_bfloat16* __restrict__ colsT, long long ldt, int B, int S, int F) {
     __shared__ float tile[32][33];
+    dnb::pdl_wait();
+    dnb::pdl_launch();
     const int r0 = blockIdx.y * 32, f0 = blockIdx.x * 32;
     const int R = B * S;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -35,6 +37,8 @@ __global__ void cast_time_major_kernel(const float* __restrict__ x, __nv_bfloat1
 __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldi,
                                       __nv_bfloat16* __restrict__ out, long long ldo, int R, int C) {
     __shared__ __nv_bfloat16 tile[32][34];
+    dnb::pdl_wait();
+    dnb::pdl_launch();
     const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         const int r = r0 + i, c = c0 + threadIdx.x;
@@ -77,7 +81,45 @@ __global__ void window_gather_kernel(const float* __restrict__ in, float* __rest
 }
 
 // K6: softmax + cross-entropy (mean over the batch) forward, and its gradient, in one pass.
-// One warp per row; classes strided over lanes.  loss accumulated with one atomic per row.
+// One warp per row; classes strided over lanes.  Small batches (the federated sites' 16-64 rows) run as ONE
+// CTA that loops over the rows and reduces the loss on-chip: no memset node, no atomics.  Larger batches
+// use one atomic per row into a zeroed scalar.
+__global__ void softmax_ce_small_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                                        float* __restrict__ prob, float* __restrict__ dlogits, float* __restrict__ loss,
+                                        int B, int ncls, int log_softmax_out) {
+    __shared__ float part[8];
+    dnb::pdl_wait();
+    dnb::pdl_launch();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const float invB = 1.f / (float)B;
+    float acc = 0.f;
+    for (int row = warp; row < B; row += nw) {
+        const float* z = logits + (long long)row * ncls;
+        float mx = -INFINITY;
+        for (int c = lane; c < ncls; c += 32) mx = fmaxf(mx, z[c]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.f;
+        for (int c = lane; c < ncls; c += 32) sum += __expf(z[c] - mx);
+        sum = dnb::warp_sum(sum);
+        const float lse = mx + __logf(sum);
+        const int y = (int)labels[row];
+        for (int c = lane; c < ncls; c += 32) {
+            const float p = __expf(z[c] - lse);
+            if (prob) prob[(long long)row * ncls + c] = log_softmax_out ? (z[c] - lse) : p;
+            if (dlogits) dlogits[(long long)row * ncls + c] = (p - (c == y ? 1.f : 0.f)) * invB;
+        }
+        acc += (lse - z[y]) * invB;
+    }
+    if (lane == 0) part[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0 && loss) {
+        float s = 0.f;
+        for (int w = 0; w < nw; ++w) s += part[w];
+        *loss = s;
+    }
+}
+
 __global__ void softmax_ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
                                   float* __restrict__ prob, float* __restrict__ dlogits, float* __restrict__ loss,
                                   int B, int ncls, int log_softmax_out) {
@@ -153,9 +195,8 @@ DNB_EXPORT int dnb_cast_time_major(const float* x, void* rows, long long ldr, vo
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(x && rows && B > 0 && S > 0 && F > 0, "dnb_cast_time_major: bad arguments");
     dim3 grid((F + 31) / 32, (B * S + 31) / 32), block(32, 8);
-    cast_time_major_kernel<<<grid, block, 0, st>>>(x, reinterpret_cast<__nv_bfloat16*>(rows), ldr,
-                                                   reinterpret_cast<__nv_bfloat16*>(colsT), ldt, B, S, F);
-    DNB_LAUNCH_CHECK();
+    DNB_CUDA_CHECK(dnb_launch(cast_time_major_kernel, grid, block, 0, st, 0, x, reinterpret_cast<__nv_bfloat16*>(rows), ldr,
+                              reinterpret_cast<__nv_bfloat16*>(colsT), ldt, B, S, F));
     dnb_count_launch(1);
     return 0;
 }
@@ -164,9 +205,8 @@ DNB_EXPORT int dnb_transpose_bf16(const void* in, long long ldi, void* out, long
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(in && out && R > 0 && C > 0, "dnb_transpose_bf16: bad arguments");
     dim3 grid((C + 31) / 32, (R + 31) / 32), block(32, 8);
-    transpose_bf16_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(in), ldi,
-                                                  reinterpret_cast<__nv_bfloat16*>(out), ldo, R, C);
-    DNB_LAUNCH_CHECK();
+    DNB_CUDA_CHECK(dnb_launch(transpose_bf16_kernel, grid, block, 0, st, 0, reinterpret_cast<const __nv_bfloat16*>(in), ldi,
+                              reinterpret_cast<__nv_bfloat16*>(out), ldo, R, C));
     dnb_count_launch(1);
     return 0;
 }
@@ -202,9 +242,14 @@ DNB_EXPORT int dnb_softmax_ce(const float* logits, const long long* labels, floa
                               int B, int ncls, int log_softmax_out, void* stream_) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(logits && labels && B > 0 && ncls > 0, "dnb_softmax_ce: bad arguments");
-    if (loss) DNB_CUDA_CHECK(cudaMemsetAsync(loss, 0, sizeof(float), st));
-    softmax_ce_kernel<<<(B + 3) / 4, 128, 0, st>>>(logits, labels, prob, dlogits, loss, B, ncls, log_softmax_out);
-    DNB_LAUNCH_CHECK();
+    if (B <= 256) {
+        DNB_CUDA_CHECK(dnb_launch(softmax_ce_small_kernel, dim3(1), dim3(256), 0, st, 0, logits, labels, prob, dlogits, loss, B,
+                                  ncls, log_softmax_out));
+    } else {
+        if (loss) DNB_CUDA_CHECK(cudaMemsetAsync(loss, 0, sizeof(float), st));
+        softmax_ce_kernel<<<(B + 3) / 4, 128, 0, st>>>(logits, labels, prob, dlogits, loss, B, ncls, log_softmax_out);
+        DNB_LAUNCH_CHECK();
+    }
     dnb_count_launch(1);
     return 0;
 }

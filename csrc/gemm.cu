@@ -97,6 +97,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    dnb::pdl_wait();      // prologue done; operands of the preceding kernel are complete and visible from here on
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -141,6 +142,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int m = m0 + q * 32 + lane;
         dnb::mbar_wait(tmem_full, 0);
         dnb::tc_fence_after();
+        if (warp == 2 && lane == 0) dnb::pdl_launch();     // only the epilogue is left: let the next kernel start up
         constexpr int CH = BN < 32 ? BN : 32;
         // ---- optional BatchNorm over the columns of each row (batch statistics, biased variance):
         // every thread owns one row with all N <= BN batch columns in TMEM, so mean/variance need no
@@ -305,8 +307,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Epi& e, int M, in
     }
     if (stages < 1) stages = 1;
     const size_t smem = (size_t)stages * L::kStageBytes + (2 * L::kStages + 1) * 8 + 16 + 1024;
-    gemm_bf16_kernel<BN><<<grid, kGemmThreads, smem, st>>>(ta, tb, e, M, N, K, per, stages);
-    DNB_LAUNCH_CHECK();
+    DNB_CUDA_CHECK(dnb_launch(gemm_bf16_kernel<BN>, grid, dim3(kGemmThreads), smem, st, 0, ta, tb, e, M, N, K, per, stages));
     dnb_count_launch(1);
     return 0;
 }

@@ -82,6 +82,8 @@ __device__ __forceinline__ float dot8(const uint4& w, const float4& x0, const fl
 constexpr int kF1Feat = 8;
 constexpr int kF1Threads = kF1Feat * 16;
 __global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a) {
+    dnb::pdl_wait();       // inputs come from the preceding kernel
+    dnb::pdl_launch();     // short kernel: let the successor get scheduled right away
     extern __shared__ float sm[];
     const int B = a.B, N0 = a.N0, ldx = N0 + 4;       // +4 floats: rows of different lanes land in different banks
     float* xs = sm;                                    // [B][ldx] dropped input
@@ -175,6 +177,8 @@ __global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a
 constexpr int kF2Feat = 16;
 constexpr int kF2Threads = kF2Feat * 16;
 __global__ void __launch_bounds__(kF2Threads) head_f2_kernel(const HeadFwdArgs a) {
+    dnb::pdl_wait();       // inputs come from the preceding kernel
+    dnb::pdl_launch();     // short kernel: let the successor get scheduled right away
     extern __shared__ float sm[];
     const int B = a.B, N1 = a.N1, N2 = a.N2, N3 = a.N3, lda = N1 + 4;
     float* s1 = sm;                        // [B][lda] layer-1 activations
@@ -230,6 +234,8 @@ __global__ void __launch_bounds__(kF2Threads) head_f2_kernel(const HeadFwdArgs a
 constexpr int kB1Feat = 16;
 constexpr int kB1Threads = kB1Feat * 16;
 __global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a) {
+    dnb::pdl_wait();       // inputs come from the preceding kernel
+    dnb::pdl_launch();     // short kernel: let the successor get scheduled right away
     extern __shared__ float sm[];
     const int B = a.B, N0 = a.N0, N1 = a.N1, N2 = a.N2, N3 = a.N3, acc_mode = a.accumulate;
     const int ldz = N2 + 1;
@@ -324,6 +330,8 @@ constexpr int kJTile = 8;
 constexpr int kKTile = 128;
 constexpr int kJSplit = 8;
 __global__ void __launch_bounds__(kB2Threads) head_b2_kernel(const HeadBwdArgs a, int n_jblocks) {
+    dnb::pdl_wait();       // inputs come from the preceding kernel
+    dnb::pdl_launch();     // short kernel: let the successor get scheduled right away
     extern __shared__ float sm[];
     const int B = a.B, N0 = a.N0, N1 = a.N1, tid = threadIdx.x;
     if ((int)blockIdx.x < n_jblocks) {
@@ -401,7 +409,7 @@ __global__ void __launch_bounds__(kB2Threads) head_b2_kernel(const HeadBwdArgs a
 int launch_head_backward(const HeadBwdArgs& a, cudaStream_t st) {
     {
         const size_t smem = ((size_t)a.B * (a.N3 + a.N2 + 1 + kB1Feat)) * sizeof(float);
-        head_b1_kernel<<<a.N1 / kB1Feat, kB1Threads, smem, st>>>(a);
+        DNB_CUDA_CHECK(dnb_launch(head_b1_kernel, dim3(a.N1 / kB1Feat), dim3(kB1Threads), smem, st, 0, a));
         DNB_LAUNCH_CHECK();
     }
     {
@@ -410,7 +418,7 @@ int launch_head_backward(const HeadBwdArgs& a, cudaStream_t st) {
         const size_t smem_k = (size_t)a.B * ((a.N1 + kJSplit - 1) / kJSplit + 1) * sizeof(float);
         const size_t smem = smem_j > smem_k ? smem_j : smem_k;
         DNB_CUDA_CHECK(cudaFuncSetAttribute(head_b2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_b2_kernel<<<n_j + n_k * kJSplit, kB2Threads, smem, st>>>(a, n_j);
+        DNB_CUDA_CHECK(dnb_launch(head_b2_kernel, dim3(n_j + n_k * kJSplit), dim3(kB2Threads), smem, st, 0, a, n_j));
         DNB_LAUNCH_CHECK();
     }
     dnb_count_launch(2);
@@ -443,13 +451,13 @@ DNB_EXPORT int dnb_head_forward(const DnbHeadFwdDesc* d, void* stream_) {
     {
         const size_t smem = (size_t)d->B * (d->N0 + 4) * sizeof(float);
         DNB_CUDA_CHECK(cudaFuncSetAttribute(head_f1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_f1_kernel<<<d->N1 / kF1Feat, kF1Threads, smem, st>>>(a);
+        DNB_CUDA_CHECK(dnb_launch(head_f1_kernel, dim3(d->N1 / kF1Feat), dim3(kF1Threads), smem, st, 0, a));
         DNB_LAUNCH_CHECK();
     }
     {
         const size_t smem = (size_t)d->B * (d->N1 + 4 + kF2Feat) * sizeof(float);
         DNB_CUDA_CHECK(cudaFuncSetAttribute(head_f2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        head_f2_kernel<<<dnb_ceil_div(d->N2, kF2Feat), kF2Threads, smem, st>>>(a);
+        DNB_CUDA_CHECK(dnb_launch(head_f2_kernel, dim3(dnb_ceil_div(d->N2, kF2Feat)), dim3(kF2Threads), smem, st, 0, a));
         DNB_LAUNCH_CHECK();
     }
     dnb_count_launch(2);

@@ -263,6 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    dnb::pdl_wait();               // on-chip prologue done; global memory from here on
     // epilogue-1 role: thread = gate row (q = warp, u = lane)
     const int grow = warp * H + cta * U + lane;
     // A operand: lane = gate row (the same row this thread owns in the epilogue), 32-bit column j =
@@ -336,6 +337,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_fwd_kernel(const FwdArgs a) 
         const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
         stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
+        if (t == a.S - 1 && tid == 0) dnb::pdl_launch();   // last step: the next kernel may start its prologue
         float px[NBE];
 #pragma unroll
         for (int b = 0; b < NBE; ++b) px[b] = px_next[b];
@@ -514,6 +516,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
     const __nv_bfloat16* W = dir ? a.Whh[1] : a.Whh[0];
     const __nv_bfloat16* WT = dir ? a.WhhT[1] : a.WhhT[0];
+    if (WT == nullptr) dnb::pdl_wait();      // this path reads global memory before the allocation below
     if (WT == nullptr) {
         const int cpr = H / 8;                            // 16-byte chunks per row
         for (int base = 0; base < 128 * cpr; base += kThreads * 8) {
@@ -550,6 +553,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
     __syncthreads();
     dnb::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    dnb::pdl_wait();               // on-chip prologue done; global memory from here on
     // A operand in TENSOR MEMORY: tile mt, lane m = hidden unit mt*128 + m, 32-bit column j2 =
     // W_hh[own gate row 2*j2, unit] | W_hh[own gate row 2*j2+1, unit] << 16 — i.e. W_hh^T restricted to
     // this CTA's gate rows, K = 128.
@@ -656,6 +660,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
         const bool stamp = a.dbg != nullptr && blockIdx.x == 0 && tid == 0 && t >= a.S / 4 && t < a.S - a.S / 4;
         stamp_n += stamp ? 1 : 0;
         DNB_STAMP(0);
+        if (t == 0 && tid == 0) dnb::pdl_launch();         // last step: the next kernel may start its prologue
         float pq[4][UPT], cv[UPT], cpv[UPT];
 #pragma unroll
         for (int j = 0; j < UPT; ++j) {
@@ -846,20 +851,7 @@ __global__ void __launch_bounds__(kThreads, 1) lstm_bwd_kernel(const BwdArgs a) 
 template <typename Args>
 int launch_cluster(void (*kernel)(const Args), const Args& args, int grid, int ncta, size_t smem, cudaStream_t st) {
     DNB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(grid, 1, 1);
-    cfg.blockDim = dim3(kThreads, 1, 1);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = ncta;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    DNB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, args));
+    DNB_CUDA_CHECK(dnb_launch(kernel, dim3(grid), dim3(kThreads), smem, st, ncta, args));
     dnb_count_launch(1);
     return 0;
 }
