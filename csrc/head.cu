@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a
             const int b = c * 16 + l;
             const float* xr = xs + (b < B ? b : 0) * ldx;
             float acc = 0.f;
-#pragma unroll 4
+#pragma unroll 12      // weight rows come from L2: keep a dozen 16-byte loads in flight per thread
             for (int k = 0; k < N0 / 8; ++k)
                 acc += dot8(w[k], *reinterpret_cast<const float4*>(xr + k * 8),
                             *reinterpret_cast<const float4*>(xr + k * 8 + 4));
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(kF2Threads) head_f2_kernel(const HeadFwdArgs a
             const int b = c * 16 + l;
             const float* xr = s1 + (b < B ? b : 0) * lda;
             float acc = 0.f;
-#pragma unroll 4
+#pragma unroll 8
             for (int k = 0; k < N1 / 8; ++k)
                 acc += dot8(w[k], *reinterpret_cast<const float4*>(xr + k * 8),
                             *reinterpret_cast<const float4*>(xr + k * 8 + 4));
@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a
         sdz2[b * ldz + k] = a.a2[idx] > 0.f ? s : 0.f;
     }
     __syncthreads();
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == gridDim.x - 1) {     // one extra block: layer-3 and bias-2 gradients, off the other blocks' path
         for (int idx = tid; idx < N3 * N2; idx += kB1Threads) {
             const int c = idx / N2, k = idx % N2;
             float s = 0.f;
@@ -270,6 +270,7 @@ __global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a
             for (int b = 0; b < B; ++b) s += sdz2[b * ldz + k];
             put(a.db2 + k, s, acc_mode);
         }
+        return;
     }
     const int j0 = blockIdx.x * kB1Feat, j = j0 + f;     // N1 % 16 == 0: every thread has a valid feature
     float dy[kChunks], xh[kChunks];
@@ -283,7 +284,7 @@ __global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a
             const bool ok = b < B;
             const float* dz = sdz2 + (ok ? b : 0) * ldz;
             float acc = 0.f;
-#pragma unroll 8
+#pragma unroll 16
             for (int k = 0; k < N2; ++k) acc += dz[k] * __bfloat162float(a.W2[(size_t)k * N1 + j]);
             const float a1v = ok ? a.a1[b * N1 + j] : 0.f;
             if (ok) sa1[b * kB1Feat + f] = a1v;
@@ -385,7 +386,7 @@ __global__ void __launch_bounds__(kB2Threads) head_b2_kernel(const HeadBwdArgs a
                 float acc[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-#pragma unroll 4
+#pragma unroll 8
                 for (int j = jb; j < je; ++j) {
                     const uint4 w = *reinterpret_cast<const uint4*>(a.W1 + (size_t)j * N0 + k);
                     const float d = dz[j - jb];
@@ -409,7 +410,7 @@ __global__ void __launch_bounds__(kB2Threads) head_b2_kernel(const HeadBwdArgs a
 int launch_head_backward(const HeadBwdArgs& a, cudaStream_t st) {
     {
         const size_t smem = ((size_t)a.B * (a.N3 + a.N2 + 1 + kB1Feat)) * sizeof(float);
-        DNB_CUDA_CHECK(dnb_launch(head_b1_kernel, dim3(a.N1 / kB1Feat), dim3(kB1Threads), smem, st, 0, a));
+        DNB_CUDA_CHECK(dnb_launch(head_b1_kernel, dim3(a.N1 / kB1Feat + 1), dim3(kB1Threads), smem, st, 0, a));
         DNB_LAUNCH_CHECK();
     }
     {

@@ -172,8 +172,9 @@ class _ICALstmFn(torch.autograd.Function):
         cls = model.classifier
         training = model.training
 
-        # 1. cast + time-major
-        xb, xT = cast_time_major(x.float(), want_transpose=True)
+        # 1. cast + time-major (the transposed copy the encoder weight gradient needs is made in the backward
+        # pass, on a side stream under the BPTT kernel, instead of here on the critical path)
+        xb, _ = cast_time_major(x.float(), want_transpose=False)
         # 2. encoder: relu(x W^T + b), plus the transposed copy the i2h weight-gradient GEMM needs
         BSp = (S * B + 7) // 8 * 8
         encT = torch.empty(E, BSp, device=x.device, dtype=torch.bfloat16)[:, :S * B]
@@ -246,7 +247,7 @@ class _ICALstmFn(torch.autograd.Function):
         ctx.model = model
         ctx.dims = (B, S, E, H, D)
         ctx.pad = pad
-        ctx.saved = (xT, enc, encT, PX, C, Hprev, whh, w_ih, head_saved)
+        ctx.saved = (xb, enc, encT, PX, C, Hprev, whh, w_ih, head_saved)
         ctx.whhT = whhT
         ctx.mark_non_differentiable(hT, cT)
         return logits, hT, cT
@@ -258,7 +259,7 @@ class _ICALstmFn(torch.autograd.Function):
             return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
         model = ctx.model
         B, S, E, H, D = ctx.dims
-        (xT, enc, encT, P, C, Hprev, whh, w_ih, head_saved) = ctx.saved
+        (xb, enc, encT, P, C, Hprev, whh, w_ih, head_saved) = ctx.saved
         ctx.saved = None
         enc_l = model.encoder[0]
         cells = list(model.lstm.lstms)
@@ -303,6 +304,7 @@ class _ICALstmFn(torch.autograd.Function):
         with torch.cuda.stream(s1):
             HprevT = transpose_bf16(Hprev)          # [D*H,  S*B]
             w_ihT = transpose_bf16(w_cat)           # [E, D*4H]
+            xT = None if capture else transpose_bf16(xb)   # [comps*window, S*B]
             ev_side = torch.cuda.Event()
             ev_side.record(s1)
 
@@ -327,7 +329,7 @@ class _ICALstmFn(torch.autograd.Function):
                 model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (delta, hp)
             d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
             gemm_bf16(dP, w_ihT, out=d_enc, mask=enc)
-            model._dad_pairs["encoder.0"] = (d_enc, xT.t())
+            model._dad_pairs["encoder.0"] = (d_enc, xb)
             if pad is not None:
                 pad.scatter_grads(model)
             return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)
