@@ -85,6 +85,13 @@ DNB_EXPORT int dnb_enable_peer_access(int peer_device) {
     return 0;
 }
 
+DNB_EXPORT int dnb_copy_async(void* dst, const void* src, size_t bytes, int kind, void* stream_) {
+    DNB_REQUIRE(dst && src && kind >= 1 && kind <= 3, "dnb_copy_async: bad arguments");
+    const cudaMemcpyKind k = kind == 1 ? cudaMemcpyHostToDevice : (kind == 2 ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice);
+    DNB_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, k, reinterpret_cast<cudaStream_t>(stream_)));
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------ TMA descriptors
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,

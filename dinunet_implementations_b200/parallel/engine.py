@@ -19,6 +19,7 @@ simulated sites on one GPU through ``SiteGroup.local`` for tests).
 from __future__ import annotations
 
 import contextlib
+import ctypes
 import os
 
 import torch
@@ -140,6 +141,7 @@ class DeviceEngine:
         self._copy_stream = None
         self._staging = None
         self._loss_ring = None
+        self._fast = None
         self._pending = []
 
     # ------------------------------------------------------------------ training
@@ -258,11 +260,19 @@ class DeviceEngine:
     def train_step_async(self, host_batch):
         """Pipelined variant for host-resident (pinned) batches: the H2D copy of this batch runs on
         a copy stream while the previous step still computes, and the loss comes back through a
-        pinned ring without stalling the launch thread.  Call ``drain()`` to collect the losses."""
+        pinned ring without stalling the launch thread.  Call ``drain()`` to collect the losses.
+
+        Host cost matters here: one GPU step is ~0.3 ms, and the obvious implementation (``.to()`` under a
+        stream context, fresh events, ``copy_`` per tensor) spent 0.34 ms of host time per step — the
+        pipeline was launch-bound.  Once the graph exists, a step is therefore a handful of raw async copies
+        through the native library into preallocated ping-pong buffers, two event records/waits on
+        persistent events, and the graph replay."""
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=self.device)
             self._staging = [None, None]
             self._loss_ring = torch.zeros(64, dtype=torch.float32).pin_memory()
+        if self._graph is not None and self._fast_ok(host_batch):
+            return self._fast_async(host_batch)
         slot = self.steps & 1
         cur = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self._copy_stream):
@@ -281,6 +291,60 @@ class DeviceEngine:
         self._loss_ring[ring_ix:ring_ix + 1].copy_(it["loss"].detach().reshape(1), non_blocking=True)
         self._pending.append(ring_ix)
         if len(self._pending) == self._loss_ring.numel():
+            return self.drain()
+        return None
+
+    def _fast_ok(self, host_batch):
+        si = self._static_in
+        for k, v in host_batch.items():
+            if isinstance(v, torch.Tensor):
+                t = si.get(k)
+                if (not isinstance(t, torch.Tensor) or v.is_cuda or not v.is_pinned() or not v.is_contiguous()
+                        or v.dtype != t.dtype or v.shape != t.shape):
+                    return False
+        return self._static_out is not None and self._static_out["loss"].dtype == torch.float32
+
+    def _fast_async(self, host_batch):
+        from ..ops import native
+        lib = native.lib()
+        fs = self._fast
+        if fs is None:
+            keys = [k for k, v in host_batch.items() if isinstance(v, torch.Tensor)]
+            fs = self._fast = {
+                "keys": keys,
+                "buf": [{k: torch.empty_like(self._static_in[k]) for k in keys} for _ in range(2)],
+                "ready": [torch.cuda.Event(), torch.cuda.Event()],
+                "consumed": [torch.cuda.Event(), torch.cuda.Event()],
+                "used": [False, False],
+                "nbytes": {k: self._static_in[k].numel() * self._static_in[k].element_size() for k in keys},
+                "static_ptr": {k: self._static_in[k].data_ptr() for k in keys},
+                "loss_ptr": self._static_out["loss"].data_ptr(),
+                "ring_ptr": self._loss_ring.data_ptr(),
+                "copy": lib.dnb_copy_async,
+            }
+            fs["copy"].argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p]
+        self.steps += 1
+        slot = self.steps & 1
+        cs = self._copy_stream
+        cur = torch.cuda.current_stream(self.device)
+        cs_h, cur_h = cs.cuda_stream, cur.cuda_stream
+        copy, buf = fs["copy"], fs["buf"][slot]
+        if fs["used"][slot]:
+            cs.wait_event(fs["consumed"][slot])          # the step that read this slot has consumed it
+        for k in fs["keys"]:
+            copy(buf[k].data_ptr(), host_batch[k].data_ptr(), fs["nbytes"][k], 1, cs_h)
+        fs["ready"][slot].record(cs)
+        cur.wait_event(fs["ready"][slot])
+        for k in fs["keys"]:
+            copy(fs["static_ptr"][k], buf[k].data_ptr(), fs["nbytes"][k], 3, cur_h)
+        fs["consumed"][slot].record(cur)                   # staging slot free again once these copies have run
+        self._graph.replay()
+        fs["used"][slot] = True
+        fs.setdefault("host_ref", [None, None])[slot] = host_batch   # keep the pinned source alive while its DMA may run
+        ring_ix = len(self._pending) % 64
+        copy(fs["ring_ptr"] + 4 * ring_ix, fs["loss_ptr"], 4, 2, cur_h)
+        self._pending.append(ring_ix)
+        if len(self._pending) == 64:
             return self.drain()
         return None
 

@@ -43,6 +43,10 @@ int dnb_ipc_get_handle(void* dptr, void* handle_out);
 int dnb_ipc_open_handle(const void* handle, void** out);
 int dnb_ipc_close_handle(void* p);
 int dnb_enable_peer_access(int peer_device);
+/* Plain asynchronous copy on `stream` (kind: 1 host->device, 2 device->host, 3 device->device).  The pipelined
+ * training step uses it to stage batches without per-step framework overhead (stream-context switches and
+ * tensor allocations cost more host time than the whole GPU step takes). */
+int dnb_copy_async(void* dst, const void* src, size_t bytes, int kind, void* stream);
 
 /* COINSTAC file mode: mean over n_src flat arrays (fp32, or fp16 when is_half) -> fp32.
  * Replaces the aggregator's multiprocessing pool (reference remote.py:20-21). */
