@@ -124,6 +124,7 @@ class Simulator:
     @classmethod
     def from_data_path(cls, comp_dir, data_path, work_dir, num_sites=None, overrides=None, verbose=False):
         """Reference-style launch: computation dir + simulator data dir."""
+        comp_dir, data_path, work_dir = (os.path.abspath(p) for p in (comp_dir, data_path, work_dir))   # inputs are sym-linked
         with open(os.path.join(data_path, "inputspec.json")) as f:
             spec = json.load(f)
         spec = spec if isinstance(spec, list) else [spec]
