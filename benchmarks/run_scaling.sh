@@ -30,9 +30,11 @@ if [ "$PART" != extra ]; then
   for n in 1 2 4 8; do [ $n -le $MAXN ] && run $n recon-nccl --steps 30 --warmup 3; done
 fi
 if [ "$PART" != main ]; then
-  port=$((29600 + RANDOM % 300))
-  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $MAXN --master-addr 127.0.0.1 --master-port $port \
-    benchmarks/agg_microbench.py > $OUT/agg_microbench_$MAXN.jsonl 2>$OUT/agg.err; tail -3 $OUT/agg_microbench_$MAXN.jsonl | cut -c1-200
+  if [ -z "${SKIP_MICRO:-}" ]; then
+    port=$((29600 + RANDOM % 300))
+    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $MAXN --master-addr 127.0.0.1 --master-port $port \
+      benchmarks/agg_microbench.py > $OUT/agg_microbench_$MAXN.jsonl 2>$OUT/agg.err; tail -3 $OUT/agg_microbench_$MAXN.jsonl | cut -c1-200
+  fi
   port=$((29600 + RANDOM % 300))
   for cfg in ica-rankdad mlp-powersgd; do
     port=$((29600 + RANDOM % 300))
