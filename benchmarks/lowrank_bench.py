@@ -162,7 +162,7 @@ def main():
                 tr.cache["agg_engine"] = "rankDAD"
             else:
                 tr = make_fs_trainer(local_rank, [4096] * 6, a.batch, "powerSGD", 4)
-            eng = DeviceEngine(tr)
+            eng = DeviceEngine(tr, use_graph=True)   # captured when the engine allows it (rankDAD with fused capture); else eager
             step = lambda b: eng.train_step(b)
         else:
             torch.manual_seed(1)

@@ -63,10 +63,24 @@ def _orth_fast(P: torch.Tensor) -> torch.Tensor:
     return orthogonalize(P)
 
 
+_SEEDED = {}
+
+
 def _seeded_normal(shape, seed, device, dtype):
+    """Seeded start matrix, identical on every site.  Drawn on the CPU generator (device independent);
+    device copies are cached — they are constants of (shape, seed), callers never modify them in place —
+    which also keeps the low-rank step free of host-to-device copies (CUDA-graph capturable)."""
+    device = torch.device(device)
+    key = (tuple(int(x) for x in shape), int(seed), device.type, device.index, dtype)
+    hit = _SEEDED.get(key)
+    if hit is not None:
+        return hit
     g = torch.Generator(device="cpu")
     g.manual_seed(int(seed) % (2 ** 31 - 1))
-    return torch.randn(*shape, generator=g, dtype=torch.float32).to(device=device, dtype=dtype)
+    v = torch.randn(*shape, generator=g, dtype=torch.float32).to(device=device, dtype=dtype)
+    if device.type == "cuda" and len(_SEEDED) < 4096:
+        _SEEDED[key] = v
+    return v
 
 
 # --------------------------------------------------------------------------- rankDAD

@@ -111,7 +111,10 @@ class DeviceEngine:
                                        num_pow_iters=int(self.cache.get("dad_num_pow_iters", 5)),
                                        tol=float(self.cache.get("dad_tol", 1e-3)), lr=lr_, optimizer=opt, momentum=mom,
                                        seed=int(self.cache.get("seed", 0)))
-            use_graph = False
+            # the device rankDAD step has no host syncs and no per-step host state (fixed iteration count,
+            # cached seeded start matrices, device-resident exchange epochs): it can live in a CUDA graph
+            # when every tapped Linear hands its pair over from the fused backward (module hooks cannot)
+            use_graph = use_graph and all(isinstance(t, CapturedTap) for t in taps)
         else:
             raise ValueError(f"unknown agg_engine {self.agg_engine!r}")
         if self.agg_engine != "dSGD":

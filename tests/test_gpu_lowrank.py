@@ -114,6 +114,31 @@ def test_device_engine_with_lowrank_aggregation_trains(engine):
     assert all(l == l for l in losses) and losses[-1] < losses[0], losses
 
 
+def test_rankdad_step_replays_as_a_cuda_graph():
+    """The device rankDAD step (fused backward hands over (delta, activation) pairs, subspace iteration,
+    factor exchange, reconstruction, optimiser) has no host syncs: it is captured once and replayed, and
+    trains like the eager engine."""
+    from dinunet_implementations_b200.parallel.engine import DeviceEngine, make_ica_trainer
+
+    def eng(use_graph):
+        tr = make_ica_trainer(0, batch_size=8, hidden_size=64, input_size=32, num_components=8, window_size=5,
+                              temporal_size=40, seed=5)
+        tr.cache["agg_engine"] = "rankDAD"
+        tr.nn["net"].classifier[0].p = 0.0
+        return DeviceEngine(tr, use_graph=use_graph, graph_warmup=2)
+    g = torch.Generator().manual_seed(1)
+    bs = [{"inputs": torch.randn(8, 8, 8, 5, generator=g), "labels": torch.randint(0, 2, (8,), generator=g)} for _ in range(10)]
+    e1, e2 = eng(False), eng(True)
+    l1 = [float(e1.train_step(b)["loss"].detach()) for b in bs]
+    l2 = [float(e2.train_step(b)["loss"].detach()) for b in bs]
+    assert e2._graph is not None, "rankDAD step must be graph-capturable"
+    assert max(abs(a - b) for a, b in zip(l1, l2)) < 5e-3, (l1, l2)
+    p1 = torch.cat([p.detach().flatten() for p in e1.params])
+    p2 = torch.cat([p.detach().flatten() for p in e2.params])
+    assert (p1 - p2).abs().mean() < 1e-3
+    e1.close(); e2.close()
+
+
 def test_fused_capture_pairs_reproduce_the_weight_gradients():
     """The (delta, activation) pairs handed over by the fused ICA-LSTM backward reconstruct the same
     gradients the fused weight-gradient GEMMs produce (delta^T . activation, bias = column sums)."""
