@@ -34,6 +34,26 @@ __global__ void cast_time_major_kernel(const float* __restrict__ x, __nv_bfloat1
     }
 }
 
+// rows only (no transposed copy), F % 8 == 0: each thread converts 8 consecutive features — two 16-byte loads,
+// one 16-byte store; consecutive threads walk along a row, so both sides are fully coalesced
+__global__ void cast_rows_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ rows, long long ldr, int B, int S,
+                                 int F8) {
+    dnb::pdl_wait();
+    dnb::pdl_launch();
+    const long long total = (long long)B * S * F8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % F8);
+        const long long r = i / F8;                       // r = t*B + b
+        const int t = (int)(r / B), b = (int)(r % B);
+        const float4* src = reinterpret_cast<const float4*>(x + (((long long)b * S + t) * F8 + c) * 8);
+        const float4 v0 = src[0], v1 = src[1];
+        uint4 o;
+        o.x = dnb::pack_bf16x2(v0.x, v0.y); o.y = dnb::pack_bf16x2(v0.z, v0.w);
+        o.z = dnb::pack_bf16x2(v1.x, v1.y); o.w = dnb::pack_bf16x2(v1.z, v1.w);
+        *reinterpret_cast<uint4*>(rows + r * ldr + (long long)c * 8) = o;
+    }
+}
+
 __global__ void transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, long long ldi,
                                       __nv_bfloat16* __restrict__ out, long long ldo, int R, int C) {
     __shared__ __nv_bfloat16 tile[32][34];
@@ -194,6 +214,14 @@ DNB_EXPORT int dnb_cast_time_major(const float* x, void* rows, long long ldr, vo
                                    int F, void* stream_) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(x && rows && B > 0 && S > 0 && F > 0, "dnb_cast_time_major: bad arguments");
+    if (colsT == nullptr && F % 8 == 0 && ldr % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)rows & 15) == 0) {
+        const long long total = (long long)B * S * (F / 8);
+        const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+        DNB_CUDA_CHECK(dnb_launch(cast_rows_kernel, dim3(blocks), dim3(256), 0, st, 0, x, reinterpret_cast<__nv_bfloat16*>(rows), ldr,
+                                  B, S, F / 8));
+        dnb_count_launch(1);
+        return 0;
+    }
     dim3 grid((F + 31) / 32, (B * S + 31) / 32), block(32, 8);
     DNB_CUDA_CHECK(dnb_launch(cast_time_major_kernel, grid, block, 0, st, 0, x, reinterpret_cast<__nv_bfloat16*>(rows), ldr,
                               reinterpret_cast<__nv_bfloat16*>(colsT), ldt, B, S, F));
