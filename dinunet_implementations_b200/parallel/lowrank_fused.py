@@ -18,6 +18,7 @@ Every object here drives all sites that live in this process: one with ``torchru
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -240,21 +241,46 @@ class DeviceRankDAD:
             if site is None or s == site:
                 self.opt[li].flat_grad.zero_()
 
+    # The layers are independent of one another and each one's subspace iteration is a strictly serial chain
+    # of tiny kernels (a few SMs each), so the per-layer work is spread over side streams: concurrent in
+    # eager mode, parallel branches when the step is captured in a CUDA graph.
+    _N_STREAMS = int(os.environ.get("DINUNET_DAD_STREAMS", "8"))
+
+    def _streams(self):
+        if getattr(self, "_side", None) is None:
+            self._side = [torch.cuda.Stream(device=self.group.device) for _ in range(self._N_STREAMS)]
+        return self._side
+
+    def _fork(self):
+        main = torch.cuda.current_stream(self.group.device)
+        side = self._streams()
+        for st in side:
+            st.wait_stream(main)
+        return main, side
+
+    @staticmethod
+    def _join(main, side):
+        for st in side:
+            main.wait_stream(st)
+
     def step(self):
         r = self.rank
         for li, s in enumerate(self.sites):
             pay = self.xf.payload[s]
             pay.zero_()                                           # other sites' slots must stay zero
             base = s * self.slot
-            for k, tap in enumerate(self.taps[li]):
-                D, A = tap.pop()
+            pairs = [tap.pop() for tap in self.taps[li]]          # on the stream that produced them
+            main, side = self._fork()
+            for k, (D, A) in enumerate(pairs):
                 o, i = self.dims[k]
-                if D is None:
-                    D, A = torch.zeros(1, o, device=pay.device), torch.zeros(1, i, device=pay.device)
-                d, a, _ = lowrank.dad_compress(D, A, r, self.iters, self.tol, self.seed + k)
-                od, oa = self.f_off[k]
-                pay[base + od: base + od + r * o].copy_(d.reshape(-1))
-                pay[base + oa: base + oa + r * i].copy_(a.reshape(-1))
+                with torch.cuda.stream(side[k % len(side)]):
+                    if D is None:
+                        D, A = torch.zeros(1, o, device=pay.device), torch.zeros(1, i, device=pay.device)
+                    d, a, _ = lowrank.dad_compress(D, A, r, self.iters, self.tol, self.seed + k)
+                    od, oa = self.f_off[k]
+                    pay[base + od: base + od + r * o].copy_(d.reshape(-1))
+                    pay[base + oa: base + oa + r * i].copy_(a.reshape(-1))
+            self._join(main, side)
             if self.xd is not None:
                 flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1)
                                   for p in self.dense[li]])
@@ -263,21 +289,24 @@ class DeviceRankDAD:
         Dm = self.xd.mean() if self.xd is not None else None
         for li, s in enumerate(self.sites):
             cat = Fm[li] * float(self.S)                          # undo the mean: plain concatenation
+            main, side = self._fork()
             for k, tap in enumerate(self.taps[li]):
                 o, i = self.dims[k]
                 od, oa = self.f_off[k]
-                ds = [cat[q * self.slot + od: q * self.slot + od + r * o].view(r, o) for q in range(self.S)]
-                as_ = [cat[q * self.slot + oa: q * self.slot + oa + r * i].view(r, i) for q in range(self.S)]
-                d, a, _ = lowrank.dad_reduce(ds, as_, r, self.iters, self.tol, self.seed + 101 * k, average=True)
-                # reconstruction GEMM  G[out, in] = d^T a  (K = r)
-                w = tap.module.weight
-                G = torch.empty(o, i, device=w.device)
-                gemm_bf16(_bf16_pad_cols(d.t().contiguous()), _bf16_pad_cols(a.t().contiguous()), out=G)
-                if tap.module.bias is not None:
-                    tap.module.bias.grad.copy_(G[:, -1])
-                    w.grad.copy_(G[:, :-1])
-                else:
-                    w.grad.copy_(G)
+                with torch.cuda.stream(side[k % len(side)]):
+                    ds = [cat[q * self.slot + od: q * self.slot + od + r * o].view(r, o) for q in range(self.S)]
+                    as_ = [cat[q * self.slot + oa: q * self.slot + oa + r * i].view(r, i) for q in range(self.S)]
+                    d, a, _ = lowrank.dad_reduce(ds, as_, r, self.iters, self.tol, self.seed + 101 * k, average=True)
+                    # reconstruction GEMM  G[out, in] = d^T a  (K = r)
+                    w = tap.module.weight
+                    G = torch.empty(o, i, device=w.device)
+                    gemm_bf16(_bf16_pad_cols(d.t().contiguous()), _bf16_pad_cols(a.t().contiguous()), out=G)
+                    if tap.module.bias is not None:
+                        tap.module.bias.grad.copy_(G[:, -1])
+                        w.grad.copy_(G[:, :-1])
+                    else:
+                        w.grad.copy_(G)
+            self._join(main, side)
             if Dm is not None:
                 off = 0
                 for p in self.dense[li]:
