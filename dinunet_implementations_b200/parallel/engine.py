@@ -87,7 +87,8 @@ class DeviceEngine:
             from .lowrank_fused import DevicePowerSGD
             self.fused = DevicePowerSGD(group, [self.params], rank=int(self.cache.get("powersgd_rank", 4)), lr=lr_,
                                         optimizer=opt, momentum=mom, seed=int(self.cache.get("seed", 0)))
-            use_graph = False            # host-side control flow between the exchange phases
+            # both exchange phases are device-side (reduce kernel with device-resident epochs) and all state
+            # (error feedback, warm-started Q) is updated in place: the step can be captured
         elif self.agg_engine == "rankDAD":
             from ..distrib.rankdad import _LinearTap
             from .lowrank_fused import DeviceRankDAD

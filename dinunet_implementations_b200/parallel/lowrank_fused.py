@@ -184,7 +184,7 @@ class DevicePowerSGD:
                 g = ps[i].grad.view(n, m)
                 gemm_bf16(_bf16_pad_cols(P_hat), _bf16_pad_cols(Qk), out=g)    # K = r (zero-filled to a k-tile)
                 self.E[li][k].sub_(g)
-                self.Q[li][k] = Qk.clone()
+                self.Q[li][k].copy_(Qk)          # in place: the warm start survives CUDA-graph replay
             for j, i in enumerate(self.vec_ix):
                 ps[i].grad.copy_(Pm[li][self.v_off[j]:self.v_off[j] + ps[i].numel()].view_as(ps[i]))
             self.opt[li].step()
