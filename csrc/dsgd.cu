@@ -45,6 +45,8 @@ struct DsgdArgs {
     float lr, beta1, beta2, eps, wd, bc1, bc2, grad_scale, momentum;
     uint32_t epoch;
     uint32_t* dev_state;   // optional {completed steps, blocks-done counter, lr bits}: makes the launch replayable
+    float* stage;          // optional fp32 local gradients to cast into grads[rank] in-kernel (16-bit wire)
+    int zero_stage;
 };
 
 __device__ __forceinline__ void flag_barrier(const DsgdArgs& a, int phase, uint32_t epoch) {
@@ -92,6 +94,21 @@ __device__ __forceinline__ void load8(const void* base, long long i, float (&x)[
     }
 }
 
+template <int WIRE>
+__device__ __forceinline__ void store8_wire(void* base, long long i, const float (&x)[8]) {
+    uint4 o;
+    if constexpr (WIRE == 1) {
+        o.x = dnb::pack_bf16x2(x[0], x[1]); o.y = dnb::pack_bf16x2(x[2], x[3]);
+        o.z = dnb::pack_bf16x2(x[4], x[5]); o.w = dnb::pack_bf16x2(x[6], x[7]);
+    } else {
+        __half2 h0 = __floats2half2_rn(x[0], x[1]), h1 = __floats2half2_rn(x[2], x[3]);
+        __half2 h2 = __floats2half2_rn(x[4], x[5]), h3 = __floats2half2_rn(x[6], x[7]);
+        o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
+        o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
+    }
+    *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(base) + i) = o;
+}
+
 __device__ __forceinline__ void store8_f32(float* base, long long i, const float (&x)[8]) {
     float4* p = reinterpret_cast<float4*>(base + i);
     p[0] = make_float4(x[0], x[1], x[2], x[3]);
@@ -113,6 +130,31 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
         bc1 = 1.f - powf(a.beta1, (float)t_dev);
         bc2 = sqrtf(1.f - powf(a.beta2, (float)t_dev));
     }
+    const long long stride = (long long)gridDim.x * blockDim.x * 8;
+    if constexpr (WIRE != 0) {
+        if (a.stage != nullptr) {
+            // Cast this rank's fp32 gradients into its peer-visible wire buffer.  Block b packs, for every
+            // peer's shard, exactly the elements that peer's block b will read (same indexing as the reduce
+            // loop below), so the per-block flag barrier is all the ordering the peers need; the local reduce
+            // re-reads only what the same thread wrote.
+            void* wire = const_cast<void*>(a.grads[a.rank]);
+            const int shards = (a.mode == 0 && a.nranks > 1) ? a.nranks : 1;
+            const long long per = shards > 1 ? ((a.n / 8 + a.nranks - 1) / a.nranks) * 8 : a.n;
+            for (int p = 0; p < shards; ++p) {
+                long long plo = per * p, phi = plo + per < a.n ? plo + per : a.n;
+                if (plo > phi) plo = phi;
+                for (long long i = plo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < phi; i += stride) {
+                    float x[8];
+                    load8<0>(a.stage, i, x);
+                    store8_wire<WIRE>(wire, i, x);
+                    if (a.zero_stage) {
+                        const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        store8_f32(a.stage, i, z);
+                    }
+                }
+            }
+        }
+    }
     if (a.use_flags) flag_barrier(a, 0, epoch);
 
     long long lo = 0, hi = a.n;
@@ -122,7 +164,6 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
         hi = lo + per < a.n ? lo + per : a.n;
         if (lo > hi) lo = hi;
     }
-    const long long stride = (long long)gridDim.x * blockDim.x * 8;
     for (long long i = lo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < hi; i += stride) {
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         // all peers' loads are issued before the first add: nranks 16-byte requests in flight
@@ -234,6 +275,8 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     a.bc2 = sqrtf(1.f - powf(d->beta2, (float)d->step));
     a.grad_scale = d->grad_scale; a.momentum = d->momentum; a.epoch = d->epoch;
     a.dev_state = d->dev_state;
+    a.stage = d->stage; a.zero_stage = d->zero_stage;
+    DNB_REQUIRE(a.stage == nullptr || d->wire != 0, "in-kernel gradient packing is for the 16-bit wire formats only");
     if (a.use_flags)
         for (int r = 0; r < d->nranks; ++r) DNB_REQUIRE(a.flags[r] != nullptr, "flags[%d] is null", r);
 

@@ -139,6 +139,7 @@ class DsgdDesc(ctypes.Structure):
         ("grad_scale", ctypes.c_float),
         ("epoch", ctypes.c_uint32),
         ("dev_state", ctypes.c_void_p),
+        ("stage", ctypes.c_void_p), ("zero_stage", ctypes.c_int),
     ]
 
 

@@ -86,6 +86,7 @@ class FusedDSGD:
             self.set_lr(self.lr)
         self._descs = None
         self._grad_staging = None   # per-site fp32 grads when the wire is 16-bit
+        self._stage_clean = False   # True once an in-kernel pack has cleared the staging gradients
         # Race-detection aid: with DINUNET_DEBUG_POISON=1 the peer-visible gradient buffer is
         # filled with NaN right after every aggregation launch.  The kernel's closing barrier guarantees
         # that all peers have finished reading it by then, and zero_grad() clears it before the next
@@ -145,13 +146,23 @@ class FusedDSGD:
             for s in ([site] if site is not None else self.sites_here()):
                 self.shadow[s].copy_(self.params[s])
 
+    @property
+    def inkernel_pack(self):
+        """16-bit wire: the aggregation kernel itself casts the fp32 staging gradients into the wire buffer and
+        clears the staging buffer for the next step (no cast launch, no zero-fill launch).  Not for several
+        simulated sites in one process: their kernels run one after the other, so every site's wire buffer has
+        to be complete before the first kernel starts."""
+        return bool(self._grad_staging) and (self.group.backend == "ipc" or self.group.nsites == 1)
+
     def pack_grads(self, site=None):
         """16-bit wire only: cast the fp32 staging gradients into the peer-visible wire buffer."""
-        if self._grad_staging:
+        if self._grad_staging and not self.inkernel_pack:
             for s in ([site] if site is not None else self.sites_here()):
                 self.grads[s].copy_(self._grad_staging[s])
 
     def zero_grad(self, site=None):
+        if self.inkernel_pack and self._stage_clean:
+            return                                  # the last aggregation left the staging gradients at zero
         for s in ([site] if site is not None else self.sites_here()):
             (self._grad_staging[s] if self._grad_staging else self.grads[s]).zero_()
 
@@ -173,6 +184,8 @@ class FusedDSGD:
         d.weight_decay, d.momentum = self.weight_decay, self.momentum
         d.grad_scale = 1.0 / (g.nsites * self.loss_scale)
         d.dev_state = self.dev_state[state_ix].data_ptr() if self.dev_state is not None else None
+        if self.inkernel_pack and self.opt != 2:
+            d.stage, d.zero_stage = self._grad_staging[site].data_ptr(), 1
         return d
 
     def step(self, lr=None):
@@ -182,6 +195,7 @@ class FusedDSGD:
             self._descs = [self._desc(s, i) for i, s in enumerate(self.sites_here())]
         self.pack_grads()
         self.t += 1
+        self._stage_clean = self.inkernel_pack and self.opt != 2
         st = native.stream()
         if self.dev_state is not None:
             # replayable launch: the kernel reads/advances the step itself; epoch base stays 0

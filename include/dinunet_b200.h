@@ -80,6 +80,10 @@ typedef struct DnbDsgdDesc {
                                            when set, step / epoch (= epoch + steps done + 1) / lr are read on the
                                            device and the step count is advanced by the kernel, so the identical
                                            launch can be replayed from a CUDA graph */
+    float* stage;                       /* optional (16-bit wire only): this rank's fp32 gradients.  The kernel casts them
+                                           into grads[rank] itself before the barrier (each block packs exactly the elements
+                                           the same-index block of every peer will read) — no separate cast launch */
+    int zero_stage;                     /* also clear `stage` while packing: the next step needs no zero-fill launch */
 } DnbDsgdDesc;
 int dnb_dsgd_fused_step(const DnbDsgdDesc* desc, void* stream);
 
