@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(kF1Threads) head_f1_kernel(const HeadFwdArgs a
         const uint64_t step = gen ? *a.drop_state : 0ull;       // advanced by launch 2 (after every CTA has read it)
         const uint32_t thr = gen ? (uint32_t)(a.drop_p * 65536.f) : 0u;
         const float keep = gen ? 1.f / (1.f - a.drop_p) : 1.f;
-#pragma unroll 4
+#pragma unroll 12      // B = 16, N0 = 384: 12 trips, all loads in flight at once
         for (int i = tid; i < B * per_row; i += kF1Threads) {
             float4 v = x4[i];
             if (d4) {

@@ -170,6 +170,8 @@ class DeviceEngine:
             loss = it["loss"]
             if self._one is None or self._one.dtype != loss.dtype or self._one.shape != loss.shape:
                 self._one = torch.ones_like(loss)          # persistent seed gradient: no fill launch per step
+                from ..ops.elementwise import UNIT_GRADS
+                UNIT_GRADS.add(self._one.data_ptr())
             loss.backward(gradient=self._one)
         with self._ph("aggregate+update"):
             self.fused.step()
