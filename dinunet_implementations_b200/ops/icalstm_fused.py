@@ -1,9 +1,16 @@
 """Fused sm_100a forward/backward of the whole ICA-LSTM (one ``autograd.Function``).
 
-Forward (7 launches): cast+time-major transpose → encoder GEMM(+bias+ReLU, +transposed copy)
-→ input-projection GEMM for all timesteps and both directions → persistent LSTM recurrence →
-classifier head.  Backward (11 launches): head → LSTM BPTT → transposes → tcgen05 weight- and
-data-gradient GEMMs (ReLU mask, bias column-sums and transposed store fused in the epilogue).
+Forward (8 launches, 6 on the critical path): time-major cast → encoder GEMM(+bias+ReLU, +transposed
+copy) → input-projection GEMM for all timesteps and both directions → persistent LSTM recurrence (the
+W_hh transposes for the BPTT kernel run beside it on a side stream) → classifier head (2 launches;
+draws its own dropout mask).  Backward (13 launches, 5 on the critical path): head (2) → LSTM BPTT (the
+transposes that do not depend on it run beside it) → K-major copy of dP → tcgen05 weight- and
+data-gradient GEMMs on three parallel streams (ReLU mask, bias column-sums and transposed store fused in
+the epilogue).  Reference math: ``comps/icalstm/models.py:69-110``.
+
+Shapes the kernels do not take natively are padded, not sent to the eager path: a per-direction hidden
+size that is not a multiple of 32 (``_Padded``: exact zero-padding, e.g. the reference inputspec's
+``hidden_size 348``) and a feature count ``comps*window`` that is not a multiple of 8 (``_pitched_copy``).
 
 Gradients are *accumulated* into ``param.grad`` (allocated on demand) — the same contract as
 autograd — and the Function returns no parameter gradients itself; the device engine points

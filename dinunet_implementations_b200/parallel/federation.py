@@ -109,7 +109,8 @@ class DeviceFederation:
         cache["task_id"] = task_id
         if agg_engine is not None:
             cache["agg_engine"] = stringify_enum(agg_engine)
-        cache["gpus"] = [self.local_rank]
+        # one site per GPU; without CUDA the same run goes through HostEngine (eager + gloo), see host_engine.py
+        cache["gpus"] = [self.local_rank] if torch.cuda.is_available() else []
         if cache.get("num_folds"):
             cache["split_ratio"] = None
         self.cache = cache
@@ -195,7 +196,11 @@ class DeviceFederation:
             p = cache["pretrained_path"]
             p = p if os.path.isabs(p) else os.path.join(self.state["baseDirectory"], p)
             trainer.load_checkpoint(full_path=p, load_optimizer_state=False)
-        engine = DeviceEngine(trainer, use_graph=self.use_graph, track_metrics=True)
+        if torch.cuda.is_available():
+            engine = DeviceEngine(trainer, use_graph=self.use_graph, track_metrics=True)
+        else:
+            from .host_engine import HostEngine
+            engine = HostEngine(trainer, track_metrics=True)
         engine.sync_shadow()
         out = {"agg_engine": cache["agg_engine"], "fold": fold, Key.TRAIN_LOG: [], Key.VALIDATION_LOG: [],
                "best_val_epoch": 0, "time_spent_on_computation": [], "cumulative_total_duration": []}
