@@ -47,6 +47,19 @@ def main():
             assert len(set(steps)) == 1, steps
         for r in range(world):
             assert os.path.exists(os.path.join(work, f"output/local{r}/simulatorRun/FS-Classification_global_results.zip"))
+    # second run: pre-training (E10) — the site with the most data trains alone first, its weights start everyone
+    work2 = os.path.join(tmp, "work_pre")
+    fed2 = DeviceFederation("FS-Classification", root, work2,
+                            overrides={"epochs": 2, "num_workers": 0, "batch_size": 8, "pretrain": True,
+                                       "pretrain_args": {"epochs": 2, "learning_rate": 0.002}})
+    res2 = fed2.run()
+    dist.barrier()
+    if rank == 0:
+        assert os.path.exists(os.path.join(work2, "output/local0/simulatorRun/FS-Classification/fold_0/pretrained_best.pt")), \
+            "site 0 has the largest split (70 subjects) and must have pre-trained"
+        assert not os.path.exists(os.path.join(work2, "output/local1/simulatorRun/FS-Classification/fold_0/pretrained_best.pt"))
+        assert len(res2) == 1 and res2[0]["best_val_epoch"] >= 1
+    if rank == 0:
         print(f"cpu federation on {world} sites: OK auc={[r['global_test_metrics'][0][1] for r in res]} steps={res[0]['steps']}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
