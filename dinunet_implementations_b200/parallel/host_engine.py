@@ -6,7 +6,10 @@ exercised where there is no GPU (multi-process, ``world_size > 1``, gloo), and s
 B200 can still run a federated job end to end.  It is not a performance path: one site per process, eager
 model, gradients averaged with ``all_reduce`` and a ``torch.optim`` step — the same update rule the fused
 dSGD kernel applies (unweighted mean over sites, then Adam/SGD; ``precision_bits 16`` rounds the
-gradients to bf16 before they are summed, like the 16-bit wire format).
+gradients to bf16 before they are summed, like the 16-bit wire format).  rankDAD and powerSGD use the
+reference math of ``distrib/lowrank.py`` with ``all_gather`` / ``all_reduce`` in place of the aggregator:
+rankDAD gathers every site's rank-r factors and re-compresses them redundantly on every rank; powerSGD
+averages P and Q with error feedback and a warm-started, identically seeded Q.
 """
 from __future__ import annotations
 
@@ -24,10 +27,27 @@ class HostEngine:
         self.cache = trainer.cache
         self.device = trainer.device["gpu"]
         self.agg_engine = str(getattr(self.cache.get("agg_engine", "dSGD"), "value", self.cache.get("agg_engine", "dSGD")))
-        if self.agg_engine != "dSGD":
-            raise NotImplementedError(f"HostEngine implements dSGD only (got {self.agg_engine!r}); the low-rank engines "
-                                      "run in device mode (CUDA) or in COINSTAC file mode (simulator)")
+        if self.agg_engine not in ("dSGD", "rankDAD", "powerSGD"):
+            raise ValueError(f"unknown agg_engine {self.agg_engine!r}")
         self.params = [p for m in trainer.nn.values() for p in m.parameters() if p.requires_grad]
+        self.seed = int(self.cache.get("seed", 0))
+        if self.agg_engine == "rankDAD":
+            from ..distrib.rankdad import _LinearTap
+            for m in trainer.nn.values():
+                if hasattr(m, "fused"):
+                    m.fused = False                    # hooks need the eager nn.Linear calls
+            self.taps = [_LinearTap(mod) for m in trainer.nn.values() for mod in m.modules()
+                         if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad]
+            covered = {id(p) for t in self.taps for p in (t.module.weight, t.module.bias) if p is not None}
+            self.dense = [p for p in self.params if id(p) not in covered]
+        elif self.agg_engine == "powerSGD":
+            from ..distrib import lowrank
+            r = int(self.cache.get("powersgd_rank", 4))
+            self.mats = [p for p in self.params if p.dim() >= 2]
+            self.vecs = [p for p in self.params if p.dim() < 2]
+            self.Q = [lowrank.psgd_init_q((p.shape[0], p.numel() // p.shape[0]), max(1, min(r, p.shape[0], p.numel() // p.shape[0])),
+                                          self.seed + 17 * i, p.device) for i, p in enumerate(self.mats)]
+            self.E = [torch.zeros(p.shape[0], p.numel() // p.shape[0], device=p.device) for p in self.mats]
         lr = float(self.cache.get("learning_rate", 1e-3))
         if str(self.cache.get("optimizer", "adam")).lower() == "sgd":
             self.opt = torch.optim.SGD(self.params, lr=lr, momentum=float(self.cache.get("momentum", 0.0)))
@@ -45,7 +65,64 @@ class HostEngine:
     def to_device(self, batch):
         return batch
 
+    def _mean_(self, t):
+        d = _dist()
+        if d is not None:
+            d.all_reduce(t)
+            t /= d.get_world_size()
+        return t
+
+    def _aggregate_rankdad(self):
+        from ..distrib import lowrank
+        d = _dist()
+        world = d.get_world_size() if d is not None else 1
+        r, iters = int(self.cache.get("dad_reduction_rank", 10)), int(self.cache.get("dad_num_pow_iters", 5))
+        tol = float(self.cache.get("dad_tol", 1e-3))
+        for k, t in enumerate(self.taps):
+            D, A = t.pop()
+            w = t.module.weight
+            n_in = w.shape[1] + (1 if t.module.bias is not None else 0)
+            if D is None:
+                D, A = torch.zeros(1, w.shape[0]), torch.zeros(1, n_in)
+            dk, ak, _ = lowrank.dad_compress(D, A, r, iters, tol, self.seed + k)
+            if d is not None:
+                ds, as_ = [torch.empty_like(dk) for _ in range(world)], [torch.empty_like(ak) for _ in range(world)]
+                d.all_gather(ds, dk.contiguous())
+                d.all_gather(as_, ak.contiguous())
+            else:
+                ds, as_ = [dk], [ak]
+            dr, ar, _ = lowrank.dad_reduce(ds, as_, r, iters, tol, self.seed + 101 * k, average=True)
+            G = lowrank.dad_reconstruct(dr, ar)
+            if t.module.bias is not None:
+                t.module.bias.grad = G[:, -1].contiguous()
+                G = G[:, :-1]
+            w.grad = G.contiguous().view_as(w)
+        for p in self.dense:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+            self._mean_(p.grad)
+
+    def _aggregate_powersgd(self):
+        from ..distrib import lowrank
+        for i, p in enumerate(self.mats):
+            g = p.grad if p.grad is not None else torch.zeros_like(p)
+            M = g.view(p.shape[0], -1) + self.E[i]
+            P = lowrank.orthogonalize(self._mean_(lowrank.psgd_p(M, self.Q[i])))
+            Qn = self._mean_(lowrank.psgd_q(M, P))
+            Mh = P @ Qn.t()
+            self.E[i] = M - Mh
+            self.Q[i] = Qn
+            p.grad = Mh.view_as(p).contiguous()
+        for v in self.vecs:
+            if v.grad is None:
+                v.grad = torch.zeros_like(v)
+            self._mean_(v.grad)
+
     def _aggregate(self):
+        if self.agg_engine == "rankDAD":
+            return self._aggregate_rankdad()
+        if self.agg_engine == "powerSGD":
+            return self._aggregate_powersgd()
         d = _dist()
         flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params])
         if self.half_wire:

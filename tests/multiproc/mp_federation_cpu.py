@@ -59,6 +59,22 @@ def main():
             "site 0 has the largest split (70 subjects) and must have pre-trained"
         assert not os.path.exists(os.path.join(work2, "output/local1/simulatorRun/FS-Classification/fold_0/pretrained_best.pt"))
         assert len(res2) == 1 and res2[0]["best_val_epoch"] >= 1
+    # the low-rank engines through the same driver: sites must stay identical, training must work
+    for eng in ("rankDAD", "powerSGD"):
+        work3 = os.path.join(tmp, "work_" + eng)
+        fed3 = DeviceFederation("FS-Classification", root, work3, agg_engine=eng,
+                                overrides={"epochs": 3, "num_workers": 0, "batch_size": 8, "patience": 10})
+        res3 = fed3.run()
+        dist.barrier()
+        if rank == 0:
+            ref = torch.load(os.path.join(work3, "output/local0/simulatorRun/FS-Classification/fold_0/latest.pt"), weights_only=False)
+            for r in range(1, world):
+                oth = torch.load(os.path.join(work3, f"output/local{r}/simulatorRun/FS-Classification/fold_0/latest.pt"), weights_only=False)
+                for name, v in ref["models"]["fs_net"].items():
+                    assert torch.allclose(v, oth["models"]["fs_net"][name], atol=1e-6), (eng, r, name)
+            log = json.load(open(os.path.join(work3, "output/remote/simulatorRun/FS-Classification/fold_0/logs.json")))
+            assert log["agg_engine"] == eng
+            assert log["train_log"][-1][0] < log["train_log"][0][0] + 0.05, (eng, log["train_log"])
     if rank == 0:
         print(f"cpu federation on {world} sites: OK auc={[r['global_test_metrics'][0][1] for r in res]} steps={res[0]['steps']}", flush=True)
     dist.barrier()
