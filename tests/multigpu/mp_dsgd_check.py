@@ -75,6 +75,28 @@ def main():
         assert all(l == l for l in losses)
         dist.barrier()
         eng.group.close()
+    # a model large enough for the two-shot (shard + push) mode with the 16-bit wire: the aggregation kernel
+    # casts its own gradients into the wire buffer, block-aligned with the peers' reads
+    tr = make_ica_trainer(local_rank, batch_size=8, hidden_size=256, input_size=128, num_components=32, window_size=10,
+                          temporal_size=80, seed=4, precision_bits="16")
+    tr.nn["net"].classifier[0].p = 0.0
+    eng = DeviceEngine(tr, use_graph=True, graph_warmup=2)
+    assert eng.fused.mode == 0 and eng.fused.inkernel_pack, (eng.fused.mode, eng.fused.inkernel_pack)
+    gen = torch.Generator().manual_seed(3000 + rank)
+    first = None
+    for i in range(8):
+        batch = {"inputs": torch.randn(8, 8, 32, 10, generator=gen), "labels": torch.randint(0, 2, (8,), generator=gen)}
+        l = float(eng.train_step(batch)["loss"].detach())
+        first = l if first is None else first
+    torch.cuda.synchronize()
+    flat = torch.cat([p.detach().flatten() for p in eng.params])
+    assert torch.isfinite(flat).all()
+    for other in gather(flat):
+        assert torch.equal(other, flat), "two-shot + in-kernel pack: sites diverged"
+    # the staging gradients are left at zero by the kernel (no zero-fill launch in the step)
+    assert float(eng.fused._grad_staging[eng.site].abs().max()) == 0.0
+    dist.barrier()
+    eng.close()
     if rank == 0:
         print("DeviceEngine multi-site: OK", flush=True)
 
