@@ -32,7 +32,7 @@ void dnb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed
 bool dnb_pdl_enabled() {
     static const bool on = [] {
         const char* e = getenv("DNB_PDL");
-        return e && e[0] == '1';      // opt-in: see common.cuh
+        return !(e && e[0] == '0');   // on unless DNB_PDL=0: see common.cuh
     }();
     return on;
 }

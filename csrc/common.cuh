@@ -40,13 +40,14 @@ void dnb_set_error(const char* fmt, ...);
 
 static inline int dnb_ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
 
-// Programmatic dependent launch (PDL), opt-in with DNB_PDL=1.  The kernels are written for it: each runs
-// its on-chip prologue (shared-memory carve-up, mbarrier init, TMEM allocation, tensor-map prefetch) BEFORE
-// dnb::pdl_wait() and touches global memory only after it, and calls dnb::pdl_launch() once its remaining
-// work is short, so the next kernel's CTAs can be scheduled and through their prologue by the time this one
-// drains.  Measured on the flagship step (CUDA-graph replay, 24 launches): 0.3199 ms with PDL vs 0.3227 ms
-// without (< 1 %: the launches inside a replayed graph are already cheap), so it stays off by default; the
-// GPU test suite passes either way.  Without the launch attribute both device calls are no-ops.
+// Programmatic dependent launch (PDL); DNB_PDL=0 turns it off.  Every kernel of the library is launched with
+// the programmatic-stream-serialization attribute and is written for it: it runs its on-chip prologue
+// (shared-memory carve-up, mbarrier init, TMEM allocation, tensor-map prefetch) BEFORE dnb::pdl_wait() and
+// touches global memory only after it, and it calls dnb::pdl_launch() once its remaining work is short, so the
+// next kernel's CTAs are scheduled and through their prologue by the time this one drains.  Inside the replayed
+// CUDA graph of the flagship step this is worth 1 % at 1 GPU (0.3199 vs 0.3227 ms) and 2.6 % at 2 GPUs
+// (0.3165 vs 0.3248 ms); the GPU test suite (single- and multi-GPU) passes either way.  Without the launch
+// attribute both device calls are no-ops.
 bool dnb_pdl_enabled();
 
 template <typename... KArgs, typename... Args>
