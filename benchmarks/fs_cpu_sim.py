@@ -46,6 +46,10 @@ if __name__ == "__main__":
         print(json.dumps({"unavailable": "test_fsl dataset (reference tree) not found"}))
         sys.exit(0)
     epochs = int(os.environ.get("FS_EPOCHS", "21"))
+    # untimed warm-up of both apps: the first optimiser step makes PyTorch import half of torch._dynamo / sympy
+    # (~5 s), which used to be billed to whichever arm ran first
+    run(os.path.join(ROOT, "computation"), data, 2, 1, "dSGD")
+    run(ref, data, 2, 1, "dSGD")
     for engine in ("dSGD", "rankDAD", "powerSGD"):
         out = {"config": "FS-MLP 66-256-128-64-32-2, batch 16, 2 sites, CPU, file mode", "engine": engine, "epochs": epochs}
         out["ours"] = run(os.path.join(ROOT, "computation"), data, 2, epochs, engine)
