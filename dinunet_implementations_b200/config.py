@@ -81,6 +81,7 @@ DEFAULT_ARGS = {
     "powersgd_rank": 4,
     "powersgd_start_iter": 0,
     "optimizer": "adam",
+    "cpu_threads": "auto",
     "verbose": False,
     "persist_logs": True,
 }
