@@ -200,6 +200,43 @@ DNB_EXPORT int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n,
 // reference's test_fsl data).  Returns the number of values parsed (negative on error); with
 // `normalise` every value is divided by the subject's own maximum, as the reference dataset does
 // (comps/fs/__init__.py:37).  Replaces a pandas.read_csv per sample per epoch.
+DNB_EXPORT int dnb_cpu_orthogonalize(float* P, long long n, int r, float eps, float rel) {
+    DNB_REQUIRE(P != nullptr && n >= 0 && r >= 1 && r <= 1024, "dnb_cpu_orthogonalize: bad arguments");
+    std::vector<double> orig(r, 0.0), dot(r, 0.0);
+    double fro = 0.0;
+    for (long long i = 0; i < n; ++i)
+        for (int c = 0; c < r; ++c) {
+            const double v = P[i * r + c];
+            orig[c] += v * v;
+        }
+    for (int c = 0; c < r; ++c) { fro += orig[c]; orig[c] = std::sqrt(orig[c]); }
+    const double scale = std::sqrt(fro) + eps;
+    for (int c = 0; c < r; ++c) {
+        double nn = 0.0;
+        for (long long i = 0; i < n; ++i) nn += (double)P[i * r + c] * P[i * r + c];
+        const double nrm = std::sqrt(nn);
+        const double thr = std::max((double)eps * scale, (double)rel * orig[c]);
+        if (nrm <= thr) {
+            for (long long i = 0; i < n; ++i) P[i * r + c] = 0.f;
+            continue;
+        }
+        const double inv = 1.0 / nrm;
+        for (int j = c + 1; j < r; ++j) dot[j] = 0.0;
+        for (long long i = 0; i < n; ++i) {
+            float* row = P + i * r;
+            const float q = (float)(row[c] * inv);
+            row[c] = q;
+            for (int j = c + 1; j < r; ++j) dot[j] += (double)q * row[j];
+        }
+        for (long long i = 0; i < n; ++i) {
+            float* row = P + i * r;
+            const double q = row[c];
+            for (int j = c + 1; j < r; ++j) row[j] = (float)(row[j] - q * dot[j]);
+        }
+    }
+    return 0;
+}
+
 DNB_EXPORT int dnb_parse_aseg(const char* path, double* out, int max_n, int normalise) {
     if (!path || !out || max_n <= 0) return -1;
     FILE* f = fopen(path, "r");

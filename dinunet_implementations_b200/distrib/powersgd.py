@@ -66,7 +66,7 @@ class PowerSGDLearner(COINNLearner):
         if phase == "P":
             shapes = [(m.shape[0], self._r(p)) for m, p in zip(self.M, self.mats)]
             Ps, off = self._unpack(flat, shapes, self.mats[0].device if self.mats else "cpu")
-            self.P_hat = [lr.orthogonalize(P) for P in Ps]
+            self.P_hat = [lr._orth_fast(P) for P in Ps]
             vec_shapes = [tuple(v.shape) for v in self.vecs]
             self.vec_grads, _ = self._unpack(flat[off:], vec_shapes, self.vecs[0].device if self.vecs else "cpu")
         elif phase == "Q":

@@ -107,7 +107,7 @@ class HostEngine:
         for i, p in enumerate(self.mats):
             g = p.grad if p.grad is not None else torch.zeros_like(p)
             M = g.view(p.shape[0], -1) + self.E[i]
-            P = lowrank.orthogonalize(self._mean_(lowrank.psgd_p(M, self.Q[i])))
+            P = lowrank._orth_fast(self._mean_(lowrank.psgd_p(M, self.Q[i])))
             Qn = self._mean_(lowrank.psgd_q(M, P))
             Mh = P @ Qn.t()
             self.E[i] = M - Mh

@@ -55,6 +55,11 @@ int dnb_cpu_mean_f32(const void* const* srcs, int n_src, long long n, int is_hal
 /* Native parser for one FreeSurfer aseg-stats file (reference comps/fs/__init__.py:33-39): returns the
  * number of values written to out (<0 on error); normalise != 0 divides by the subject's maximum. */
 int dnb_parse_aseg(const char* path, double* out, int max_n, int normalise);
+/* Host-side modified Gram-Schmidt of the r columns of P [n, r] (row-major fp32, in place; fp64 accumulation) with the
+ * same dead-column rule as the CUDA kernel and distrib/lowrank.orthogonalize: a column whose residual norm is
+ * <= max(eps * ||P||_F, rel * its original norm) is zeroed.  The file-mode rankDAD / powerSGD reducers call it
+ * thousands of times per run on 10-column factors; the Python loop was 40 % of a simulated rankDAD run. */
+int dnb_cpu_orthogonalize(float* P, long long n, int r, float eps, float rel);
 
 /* ---- K1: dSGD all-reduce fused with Adam/SGD (reference engine "dSGD", comps/__init__.py:14;
  *      precision_bits compspec.json:161-176) ----------------------------------------------- */
