@@ -82,6 +82,7 @@ DEFAULT_ARGS = {
     "powersgd_start_iter": 0,
     "optimizer": "adam",
     "cpu_threads": "auto",
+    "profile_enabled": False,
     "verbose": False,
     "persist_logs": True,
 }
@@ -93,7 +94,7 @@ SHARED_ARGS = [
     "learning_rate", "epochs", "validation_epochs", "precision_bits", "patience",
     "split_ratio", "num_folds", "pretrain", "pretrain_args", "monitor_metric",
     "metric_direction", "log_header", "seed", "dad_reduction_rank", "dad_num_pow_iters",
-    "dad_tol", "powersgd_rank", "optimizer",
+    "dad_tol", "powersgd_rank", "optimizer", "profile_enabled",
 ]
 
 

@@ -21,6 +21,7 @@ import numpy as np
 import torch
 
 from ..config import AggEngine
+from ..utils.profiler import timed
 
 
 def trainable_params(nn: dict):
@@ -74,6 +75,7 @@ class COINNLearner:
         for p in self.params:
             p.grad = None
 
+    @timed("learner_backward")
     def backward(self):
         self.trainer.train_mode()
         self.zero_grad()

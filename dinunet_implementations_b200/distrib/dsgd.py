@@ -12,12 +12,14 @@ from __future__ import annotations
 
 from . import COINNLearner, COINNReducer, flat_grads, assign_flat_grads
 from . import fileio
+from ..utils.profiler import timed
 
 GRADS_FILE = "grads.npy"
 AVG_GRADS_FILE = "avg_grads.npy"
 
 
 class DSGDLearner(COINNLearner):
+    @timed("learner_step")
     def step(self):
         out = {}
         name = self.input.get("avg_grads_file")
@@ -26,6 +28,7 @@ class DSGDLearner(COINNLearner):
             self.optimizer_step()
         return out
 
+    @timed("learner_to_reduce")
     def to_reduce(self):
         its = self.backward()
         out = {}
@@ -37,6 +40,7 @@ class DSGDLearner(COINNLearner):
 
 
 class DSGDReducer(COINNReducer):
+    @timed("reducer_reduce")
     def reduce(self):
         sites = sorted(self.input.keys())
         paths = [self.site_file(s, self.input[s]["grads_file"]) for s in sites]

@@ -18,6 +18,7 @@ import torch
 from . import COINNLearner, fileio
 from . import lowrank as lr
 from .dsgd import DSGDReducer
+from ..utils.profiler import timed
 
 P_FILE = "psgd_p.npy"
 Q_FILE = "psgd_q.npy"
@@ -57,6 +58,7 @@ class PowerSGDLearner(COINNLearner):
         return out, off
 
     # -- protocol ---------------------------------------------------------------------
+    @timed("learner_step")
     def step(self):
         phase = self.input.get("psgd_phase")
         name = self.input.get("avg_grads_file")
@@ -82,6 +84,7 @@ class PowerSGDLearner(COINNLearner):
             self.M = self.P_hat = self.vec_grads = None
         return {}
 
+    @timed("learner_to_reduce")
     def to_reduce(self):
         bits = self.cache.get("precision_bits", "32")
         if self.P_hat is not None and self.M is not None:
@@ -103,6 +106,7 @@ class PowerSGDLearner(COINNLearner):
 
 
 class PowerSGDReducer(DSGDReducer):
+    @timed("reducer_reduce")
     def reduce(self):
         out = super().reduce()
         phases = {self.input[s].get("psgd_phase") for s in self.input}

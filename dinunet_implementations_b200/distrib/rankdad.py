@@ -21,6 +21,7 @@ import torch
 
 from . import COINNLearner, COINNReducer, fileio
 from . import lowrank as lr
+from ..utils.profiler import timed
 
 DAD_FILE = "dad_factors.npz"
 DAD_AVG_FILE = "dad_reduced.npz"
@@ -78,6 +79,7 @@ class DADLearner(COINNLearner):
                         covered.add(id(mod.bias))
         self.dense_params = [p for p in self.params if id(p) not in covered]
 
+    @timed("learner_step")
     def step(self):
         name = self.input.get("dad_reduced_file")
         if not name:
@@ -102,6 +104,7 @@ class DADLearner(COINNLearner):
         self.optimizer_step()
         return {}
 
+    @timed("learner_to_reduce")
     def to_reduce(self):
         its = self.backward()
         if not its:
@@ -131,6 +134,7 @@ def _reduce_layer(ds, as_, rank, iters, tol, seed):
 
 
 class DADReducer(COINNReducer):
+    @timed("reducer_reduce")
     def reduce(self):
         sites = sorted(self.input.keys())
         payloads = [fileio.load_arrays(self.site_file(s, self.input[s]["dad_file"])) for s in sites]
