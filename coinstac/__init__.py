@@ -39,9 +39,9 @@ def start(local_fn, remote_fn):
         line = line.strip()
         if not line:
             continue
-        msg = json.loads(line)
-        fn = remote_fn if msg.get("mode") == "remote" else local_fn
         try:
+            msg = json.loads(line)
+            fn = remote_fn if msg.get("mode") == "remote" else local_fn
             res = fn(msg["data"])
             sys.stdout.write(json.dumps(clean_json(res)) + "\n")
         except Exception as e:  # report, keep serving
