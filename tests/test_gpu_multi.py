@@ -11,11 +11,18 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _free_port():
+    import socket
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return str(s.getsockname()[1])
+
+
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 def test_fused_dsgd_over_ipc_two_sites():
     n = min(torch.cuda.device_count(), 4)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
-           "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests/multigpu/mp_dsgd_check.py")]
+           "--master-addr", "127.0.0.1", "--master-port", _free_port(), os.path.join(ROOT, "tests/multigpu/mp_dsgd_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "raw fused dSGD over IPC: OK" in r.stdout and "DeviceEngine multi-site: OK" in r.stdout
@@ -27,7 +34,7 @@ def test_device_federation_across_gpus(tmp_path):
     n = min(torch.cuda.device_count(), 4)
     env = dict(os.environ, FED_TMP=str(tmp_path))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
-           "--master-addr", "127.0.0.1", "--master-port", "29534", os.path.join(ROOT, "tests/multigpu/mp_federation_check.py")]
+           "--master-addr", "127.0.0.1", "--master-port", _free_port(), os.path.join(ROOT, "tests/multigpu/mp_federation_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count(": OK") == 3, r.stdout[-2000:]
