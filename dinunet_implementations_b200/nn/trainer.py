@@ -90,7 +90,12 @@ class NNTrainer:
         for name in list(self.nn.keys()):
             self.nn[name] = self.nn[name].to(self.device["gpu"])
             if self.device["gpu"].type == "cuda" and len(gpus) >= 2:
-                # intra-site data parallelism, as in the reference engine
+                # intra-site data parallelism, as in the reference engine.  DataParallel replicates
+                # the module per device and reduces autograd gradients back; the fused kernels accumulate into
+                # ``param.grad`` of whatever module object they are called on, so replicas take the eager path.
+                for sub in self.nn[name].modules():
+                    if hasattr(sub, "fused"):
+                        sub.fused = False
                 self.nn[name] = torch.nn.DataParallel(self.nn[name], device_ids=[int(g) for g in gpus])
 
     def _init_optimizer(self):
