@@ -235,6 +235,62 @@ int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, lo
 int dnb_orthogonalize_batch(float* const* P, const int* n, const int* r, const int* ld, int count, float eps,
                             void* stream);
 
+/* ---- K2a / K2b: device-mode rankDAD (engine "rankDAD", reference comps/__init__.py:15; tunables
+ * dad_reduction_rank / dad_num_pow_iters, compspec.json:236-238).  One launch per call, one thread-block
+ * cluster per tapped Linear layer.
+ *   mode 0: rank-r subspace iteration on (delta [N,out], act [N,in]) -> U [out,16], V [in,16] with
+ *           delta^T act ~= U V^T (columns >= rank_cols are zero); the tail stores the factors and the dense
+ *           gradients into slot `rank` of every site's factor buffer (P2P stores) and raises a flag per peer.
+ *   mode 1: waits for all sites' flags, stacks the received factors ([nsplit*nranks*16, .] bf16 operands built
+ *           by the kernel in the workspace passed as A/AT/D/DT), re-compresses the stack to rank r, and
+ *           writes G = grad_scale * U V^T [out,in] (fp32) to layer.G; dense gradients are averaged into flat_grad.
+ * Every big operand is needed in both orientations (bf16, leading dimensions multiples of 8).  The iterates
+ * ZN/ZI/ZO/V0 are [32, ld] bf16 (16 hi rows + 16 lo rows); V0 is the seeded start matrix (identical on all sites).
+ * Limits: out <= DNB_DAD_MAX_OUT per layer, <= DNB_DAD_MAX_LAYERS layers per call, rank <= 16.
+ * dad_tol is not evaluated on the device: all `iters` iterations always run. */
+#define DNB_DAD_R 16
+#define DNB_DAD_MAX_LAYERS 8
+#define DNB_DAD_MAX_OUT 1152
+#define DNB_DAD_MAX_SPANS 32
+#define DNB_DAD_MAX_PACK 8
+typedef struct DnbDadLayerDesc {
+    const void *A, *AT, *D, *DT;          /* bf16: act [N,in], act^T [in,N], delta [N,out], delta^T [out,N] */
+    long long lda, ldat, ldd, lddt;
+    int N, in, out, pad_;
+    void *ZN, *ZI, *ZO;                   /* iterate workspaces [32, ldzn|ldzi|ldzo] bf16 */
+    const void* V0;                       /* [32, ldzi] bf16 seeded start (hi rows 0-15, lo rows 16-31) */
+    long long ldzn, ldzi, ldzo;
+    float *W, *U, *V;                     /* fp32 [out,16] scratch, [out,16] left factor, [in,16] right factor */
+    long long fact_off;                   /* float offset of this layer's (U,V) inside a site's slot */
+    void *Uc, *Vc;                        /* mode 1: bf16 [out,64] / [in,64] hi|lo stacks (workspace) */
+    float* G; long long ldg;              /* mode 1: gradient destination [out,in] */
+} DnbDadLayerDesc;
+typedef struct DnbDadDesc {
+    DnbDadLayerDesc layer[DNB_DAD_MAX_LAYERS];
+    float* fact[DNB_MAX_RANKS];           /* every site's factor buffer [2][nranks][slot_floats] fp32, peer-mapped */
+    uint32_t* flags[DNB_MAX_RANKS];       /* every site's flag words [nranks], zero-initialised, peer-mapped */
+    long long slot_floats, dense_off;     /* floats per site slot; offset of the dense gradients inside it */
+    long long span_off[DNB_DAD_MAX_SPANS];/* dense gradients = spans of flat_grad (float offsets / lengths) */
+    int span_len[DNB_DAD_MAX_SPANS];
+    float* flat_grad;
+    uint32_t* dev_state;                  /* device words {generation, CTA counter}; required with use_flags */
+    float grad_scale;                     /* mode 1: 1 / nranks */
+    int n_layers, mode, iters, cluster, nsplit, nranks, rank, use_flags, n_spans, rank_cols;
+} DnbDadDesc;
+int dnb_dad_step(const DnbDadDesc* desc, void* stream);
+
+/* fp32 [N,d] (leading dimension lds) -> bf16 row-major [N,ldr] and/or its transpose [d,ldt]; up to
+ * DNB_DAD_MAX_PACK matrices per launch (the classifier-head (delta, activation) pairs of the rankDAD step). */
+typedef struct DnbDadPackDesc {
+    const float* src[DNB_DAD_MAX_PACK];
+    void* rows[DNB_DAD_MAX_PACK];
+    void* colsT[DNB_DAD_MAX_PACK];
+    long long lds[DNB_DAD_MAX_PACK], ldr[DNB_DAD_MAX_PACK], ldt[DNB_DAD_MAX_PACK];
+    int N[DNB_DAD_MAX_PACK], d[DNB_DAD_MAX_PACK];
+    int count;
+} DnbDadPackDesc;
+int dnb_dad_pack(const DnbDadPackDesc* desc, void* stream);
+
 /* K9: device-side metric accumulators (reference hooks: new_metrics().add / new_averages().add,
  * comps/fs/__init__.py:58-61, comps/icalstm/__init__.py:64-68).  Appends column `col` of scores_in [B, ld]
  * and the labels to scores/labs (capacity cap), updates state = {cursor, tp, fp, tn, fn} (uint64) at
