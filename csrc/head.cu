@@ -44,6 +44,7 @@ struct HeadBwdArgs {
     const float* bn_w;
     float *dW1, *db1, *dbn_w, *dbn_b, *dW2, *db2, *dW3, *db3, *dx;
     float* dz1;                              // [B,N1] scratch between the two backward launches
+    float* dz2;                              // optional [B,N2]: gradient at the second layer's pre-activation (rankDAD pairs)
     int training, accumulate;
     int B, N0, N1, N2, N3;
 };
@@ -270,6 +271,8 @@ __global__ void __launch_bounds__(kB1Threads) head_b1_kernel(const HeadBwdArgs a
             for (int b = 0; b < B; ++b) s += sdz2[b * ldz + k];
             put(a.db2 + k, s, acc_mode);
         }
+        if (a.dz2 != nullptr)
+            for (int idx = tid; idx < B * N2; idx += kB1Threads) a.dz2[idx] = sdz2[(idx / N2) * ldz + idx % N2];
         return;
     }
     const int j0 = blockIdx.x * kB1Feat, j = j0 + f;     // N1 % 16 == 0: every thread has a valid feature
@@ -475,7 +478,7 @@ DNB_EXPORT int dnb_head_backward(const DnbHeadBwdDesc* d, void* stream_) {
     a.W1 = (const __nv_bfloat16*)d->W1; a.W2 = (const __nv_bfloat16*)d->W2; a.W3 = (const __nv_bfloat16*)d->W3;
     a.bn_w = d->bn_w;
     a.dW1 = d->dW1; a.db1 = d->db1; a.dbn_w = d->dbn_w; a.dbn_b = d->dbn_b; a.dW2 = d->dW2; a.db2 = d->db2;
-    a.dW3 = d->dW3; a.db3 = d->db3; a.dx = d->dx; a.dz1 = d->dz1;
+    a.dW3 = d->dW3; a.db3 = d->db3; a.dx = d->dx; a.dz1 = d->dz1; a.dz2 = d->dz2;
     a.training = d->training; a.accumulate = d->accumulate;
     a.B = d->B; a.N0 = d->N0; a.N1 = d->N1; a.N2 = d->N2; a.N3 = d->N3;
     DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&
@@ -559,6 +562,7 @@ DNB_EXPORT int dnb_head_backward_noalloc(const DnbHeadBwdDesc* d, void* stream_)
     a.dW1 = d->dW1; a.db1 = d->db1; a.dbn_w = d->dbn_w; a.dbn_b = d->dbn_b; a.dW2 = d->dW2; a.db2 = d->db2;
     a.dW3 = d->dW3; a.db3 = d->db3; a.dx = d->dx;
     a.dz1 = scratch;                                   // device address, never the host-side symbol
+    a.dz2 = d->dz2;
     a.training = d->training; a.accumulate = d->accumulate;
     a.B = d->B; a.N0 = d->N0; a.N1 = d->N1; a.N2 = d->N2; a.N3 = d->N3;
     DNB_REQUIRE(a.dlogits && a.a0 && a.xhat && a.invstd && a.a1 && a.a2 && a.dW1 && a.db1 && a.dbn_w && a.dbn_b &&

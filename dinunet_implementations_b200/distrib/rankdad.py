@@ -28,38 +28,94 @@ DAD_AVG_FILE = "dad_reduced.npz"
 
 
 class _LinearTap:
-    """Forward hook on one ``nn.Linear`` that also taps the gradient of its output."""
+    """Forward hook on one ``nn.Linear`` that also taps the gradient of its output.
+
+    Every call of the module registers its own gradient hook that remembers that call's input, so an
+    activation is always paired with the delta of the same call — whatever the order in which autograd
+    visits the calls (time loops, ``local_iterations`` > 1 micro-batches, a reused module)."""
 
     def __init__(self, module: torch.nn.Linear):
         self.module = module
-        self.acts, self.deltas = [], []
+        self.pairs = []
+        self.calls = 0
         self.h1 = module.register_forward_hook(self._fwd)
 
     def _fwd(self, mod, inp, out):
         if mod.training and torch.is_grad_enabled() and out.requires_grad:
             x = inp[0].detach()
-            self.acts.append(x.reshape(-1, x.shape[-1]))
-            out.register_hook(self._bwd)
+            x = x.reshape(-1, x.shape[-1])
+            self.calls += 1
 
-    def _bwd(self, g):
-        g = g.detach()
-        self.deltas.append(g.reshape(-1, g.shape[-1]))
+            def _bwd(g, x=x):
+                g = g.detach()
+                self.pairs.append((g.reshape(-1, g.shape[-1]), x))
+            out.register_hook(_bwd)
 
-    def pop(self):
-        # backward visits calls in reverse order of forward
-        acts = self.acts
-        deltas = self.deltas[::-1]
-        self.acts, self.deltas = [], []
-        if not acts or len(acts) != len(deltas):
+    def pop(self, with_ones=True):
+        """``(delta [N,out], act [N,in(+1)])`` of every call since the last pop, stacked along N (fp32);
+        ``(None, None)`` when the module was not used."""
+        pairs, self.pairs, self.calls = self.pairs, [], 0
+        if not pairs:
             return None, None
-        A = torch.cat(acts, 0).float()
-        D = torch.cat(deltas, 0).float()
-        if self.module.bias is not None:
+        D = torch.cat([d for d, _ in pairs], 0).float()
+        A = torch.cat([a for _, a in pairs], 0).float()
+        if with_ones and self.module.bias is not None:
+            A = torch.cat([A, torch.ones(A.shape[0], 1, device=A.device)], 1)
+        return D, A
+
+    def pop_entries(self):
+        """Device-mode protocol: list of ``{"D": delta, "A": act}`` blocks (no ones column)."""
+        pairs, self.pairs, self.calls = self.pairs, [], 0
+        return [{"D": d, "A": a} for d, a in pairs]
+
+    def remove(self):
+        self.h1.remove()
+
+
+class CapturedTap:
+    """Stands in for ``_LinearTap`` when a fused model hands over the (delta, activation) pair of a
+    Linear directly: its backward appends ``{"D","A"[,"DT","AT"]}`` blocks to ``model._dad_pairs[key]``
+    (one per backward call, so micro-batches stack), and no module hooks or eager forward are needed."""
+
+    def __init__(self, module: torch.nn.Linear, model: torch.nn.Module, key: str):
+        self.module, self.model, self.key = module, model, key
+
+    def pop_entries(self):
+        pairs = getattr(self.model, "_dad_pairs", None) or {}
+        return pairs.pop(self.key, [])
+
+    def pop(self, with_ones=True):
+        ent = self.pop_entries()
+        if not ent:
+            return None, None
+        D = torch.cat([e["D"].float() for e in ent], 0)
+        A = torch.cat([e["A"].float() for e in ent], 0)
+        if with_ones and self.module.bias is not None:
             A = torch.cat([A, torch.ones(A.shape[0], 1, device=A.device)], 1)
         return D, A
 
     def remove(self):
-        self.h1.remove()
+        pass
+
+
+def make_taps(nn_modules):
+    """``(taps, covered_param_ids)`` for every trainable ``nn.Linear`` of the given models.  A model whose
+    fused path bypasses its Linear modules (custom autograd Functions: hooks would never fire) either hands
+    the pairs over itself (``dad_capture_keys()`` → ``CapturedTap``) or is switched to its eager path."""
+    taps, covered = [], set()
+    for m in nn_modules:
+        keys = set(m.dad_capture_keys()) if (getattr(m, "fused", False) and hasattr(m, "dad_capture_keys")) else set()
+        if keys:
+            m._dad_capture = True
+        elif hasattr(m, "fused"):
+            m.fused = False
+        for name, mod in m.named_modules():
+            if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad:
+                taps.append(CapturedTap(mod, m, name) if name in keys else _LinearTap(mod))
+                covered.add(id(mod.weight))
+                if mod.bias is not None:
+                    covered.add(id(mod.bias))
+    return taps, covered
 
 
 class DADLearner(COINNLearner):
@@ -68,15 +124,7 @@ class DADLearner(COINNLearner):
         self.rank = int(self.cache.get("dad_reduction_rank", 10))
         self.iters = int(self.cache.get("dad_num_pow_iters", 5))
         self.tol = float(self.cache.get("dad_tol", 1e-3))
-        self.taps = []
-        covered = set()
-        for m in self.trainer.nn.values():
-            for mod in m.modules():
-                if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad:
-                    self.taps.append(_LinearTap(mod))
-                    covered.add(id(mod.weight))
-                    if mod.bias is not None:
-                        covered.add(id(mod.bias))
+        self.taps, covered = make_taps(self.trainer.nn.values())
         self.dense_params = [p for p in self.params if id(p) not in covered]
 
     @timed("learner_step")
@@ -114,7 +162,12 @@ class DADLearner(COINNLearner):
         for i, tap in enumerate(self.taps):
             D, A = tap.pop()
             w = tap.module.weight
-            if D is None:  # layer unused this step
+            if D is None:
+                # a Linear that took no part in this step's graph: its gradient is genuinely zero.  Anything else
+                # (hooks bypassed by a fused path, say) must not be papered over with zero factors.
+                if w.grad is not None and bool((w.grad != 0).any()):
+                    raise RuntimeError(f"rankDAD: no (delta, activation) pair was captured for Linear #{i} "
+                                       f"{tuple(w.shape)} although it has a gradient")
                 n_in = w.shape[1] + (1 if tap.module.bias is not None else 0)
                 D, A = torch.zeros(1, w.shape[0]), torch.zeros(1, n_in)
             d, a, _ = lr.dad_compress(D, A, self.rank, self.iters, self.tol, seed + i)

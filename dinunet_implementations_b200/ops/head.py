@@ -53,7 +53,7 @@ def head_forward(x, drop, W1, b1, bn_w, bn_b, run_mean, run_var, W2, b2, W3, b3,
     return logits, saved
 
 
-def head_backward(dlogits, saved, grads, accumulate=True):
+def head_backward(dlogits, saved, grads, accumulate=True, want_dz2=False):
     """``grads``: dict with fp32 tensors ``dW1 db1 dbn_w dbn_b dW2 db2 dW3 db3``.  Returns ``dx``."""
     lib = native.require_gpu()
     B, N0, N1, N2, N3 = saved["dims"]
@@ -70,8 +70,12 @@ def head_backward(dlogits, saved, grads, accumulate=True):
     d.dx = dx.data_ptr()
     dz1 = torch.empty(B, N1, device=dlogits.device)
     d.dz1 = dz1.data_ptr()
+    if want_dz2:
+        saved["dz2"] = torch.empty(B, N2, device=dlogits.device)
+        d.dz2 = saved["dz2"].data_ptr()
     d.training, d.accumulate = int(saved["training"]), int(accumulate)
     d.B, d.N0, d.N1, d.N2, d.N3 = B, N0, N1, N2, N3
     native.check(lib.dnb_head_backward(ctypes.byref(d), native.stream()), "dnb_head_backward")
     saved["dz1"] = dz1          # gradient at the BatchNorm input (rankDAD capture reads it)
+    saved["dlogits32"] = dlogits
     return dx

@@ -283,18 +283,16 @@ class _ICALstmFn(torch.autograd.Function):
                      db1=_grad_buf(cls[1].bias), dbn_w=_grad_buf(bn.weight),
                      dbn_b=_grad_buf(bn.bias), dW2=_grad_buf(cls[4].weight), db2=_grad_buf(cls[4].bias),
                      dW3=_grad_buf(cls[6].weight), db3=_grad_buf(cls[6].bias))
-        dHmean = head_backward(dlogits, head_saved, grads, accumulate=True)
+        dHmean = head_backward(dlogits, head_saved, grads, accumulate=True, want_dz2=capture)
         if capture:
-            # rankDAD: ship factors of (delta, activation) instead of the weight gradients.  The head is
-            # tiny (batch rows only), so its pairs are rebuilt from the saved activations with torch ops.
+            # rankDAD: ship factors of (delta, activation) instead of the weight gradients.  The head pairs are
+            # fp32 tensors the head kernels already produced (dz1 / dz2 are exported by the backward launches);
+            # the aggregation step packs them to bf16 in both orientations with one launch (dnb_dad_pack).
             hs = head_saved
-            B_ = dlogits.shape[0]
-            dl = dlogits.float()
-            dz2 = (dl @ hs["W3"].float()) * (hs["a2"] > 0)
-            pairs = {"classifier.6": (dl, hs["a2"]), "classifier.4": (dz2, hs["a1"])}
-            # dz1 is what head_backward handed from its first to its second launch
-            pairs["classifier.1"] = (hs["dz1"], hs["a0"] if pad is None else pad.unpad(hs["a0"]))
-            model._dad_pairs = pairs
+            pairs = model.__dict__.setdefault("_dad_pairs", {})
+            pairs.setdefault("classifier.6", []).append({"D": hs["dlogits32"], "A": hs["a2"]})
+            pairs.setdefault("classifier.4", []).append({"D": hs["dz2"], "A": hs["a1"]})
+            pairs.setdefault("classifier.1", []).append({"D": hs["dz1"], "A": hs["a0"] if pad is None else pad.unpad(hs["a0"])})
 
         # Independent pieces of the backward run on side streams (parallel branches when the step is
         # captured in a CUDA graph): the transposes that do not depend on dP hide under the BPTT kernel
@@ -311,7 +309,7 @@ class _ICALstmFn(torch.autograd.Function):
         with torch.cuda.stream(s1):
             HprevT = transpose_bf16(Hprev)          # [D*H,  S*B]
             w_ihT = transpose_bf16(w_cat)           # [E, D*4H]
-            xT = None if capture else transpose_bf16(xb)   # [comps*window, S*B]
+            xT = transpose_bf16(xb)                 # [comps*window, S*B]
             ev_side = torch.cuda.Event()
             ev_side.record(s1)
 
@@ -326,17 +324,32 @@ class _ICALstmFn(torch.autograd.Function):
         ev_dp.record(main)
 
         if capture:
-            # LSTM pairs: delta = dP (per direction), activations = encoder output / previous hidden state
-            main.wait_event(ev_side)
+            # LSTM / encoder pairs: every (delta, activation) matrix in both orientations, bf16, exactly the
+            # operands the weight-gradient GEMMs of the dSGD path consume — the rankDAD kernels take their place.
+            BSp = (S * B + 7) // 8 * 8
+            s2.wait_event(ev_dp)
+            s2.wait_event(ev_side)
+            with torch.cuda.stream(s2):
+                d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
+                d_encT = torch.empty(E, BSp, device=dev, dtype=torch.bfloat16)[:, :S * B]
+                gemm_bf16(dP, w_ihT, out=d_enc, out_t=d_encT, mask=enc, colsum=_grad_buf(enc_l.bias))
+            dPT = transpose_bf16(dP)                # [D*4H, S*B]
+            main.wait_stream(s1)
+            main.wait_stream(s2)
             for dd in range(D):
                 sl = slice(dd * 4 * H, (dd + 1) * 4 * H)
-                delta = dP[:, sl] if pad is None else pad.gates(dP, dd)
-                hp = Hprev[:, dd * H:(dd + 1) * H] if pad is None else Hprev[:, dd * H:dd * H + pad.H]
-                model._dad_pairs[f"lstm.lstms.{dd}.i2h"] = (delta, enc)
-                model._dad_pairs[f"lstm.lstms.{dd}.h2h"] = (delta, hp)
-            d_enc = torch.empty(S * B, E, device=dev, dtype=torch.bfloat16)
-            gemm_bf16(dP, w_ihT, out=d_enc, mask=enc)
-            model._dad_pairs["encoder.0"] = (d_enc, xb)
+                if pad is None:
+                    delta, deltaT = dP[:, sl], dPT[sl]
+                    hp, hpT = Hprev[:, dd * H:(dd + 1) * H], HprevT[dd * H:(dd + 1) * H]
+                    e_ih = {"D": delta, "DT": deltaT, "A": enc, "AT": encT}
+                    e_hh = {"D": delta, "DT": deltaT, "A": hp, "AT": hpT}
+                else:       # zero-padded hidden units: hand over compact copies (packed by the aggregation step)
+                    delta = pad.gates(dP, dd)
+                    e_ih = {"D": delta, "A": enc}
+                    e_hh = {"D": delta, "A": Hprev[:, dd * H:dd * H + pad.H]}
+                pairs.setdefault(f"lstm.lstms.{dd}.i2h", []).append(e_ih)
+                pairs.setdefault(f"lstm.lstms.{dd}.h2h", []).append(e_hh)
+            pairs.setdefault("encoder.0", []).append({"D": d_enc, "DT": d_encT, "A": xb, "AT": xT})
             if pad is not None:
                 pad.scatter_grads(model)
             return (None, None) + (None,) * (len(ctx.needs_input_grad) - 2)

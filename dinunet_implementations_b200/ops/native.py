@@ -229,6 +229,7 @@ class HeadBwdDesc(ctypes.Structure):
         ("dx", ctypes.c_void_p), ("dz1", ctypes.c_void_p),
         ("training", ctypes.c_int), ("accumulate", ctypes.c_int),
         ("B", ctypes.c_int), ("N0", ctypes.c_int), ("N1", ctypes.c_int), ("N2", ctypes.c_int), ("N3", ctypes.c_int),
+        ("dz2", ctypes.c_void_p),
     ]
 
 
@@ -239,3 +240,53 @@ def vp(t):
 
 def ll(v):
     return ctypes.c_longlong(int(v))
+
+
+# ---- rankDAD device kernels (csrc/dad.cu) ---------------------------------------------------------------
+DAD_R = 16
+DAD_MAX_LAYERS = 8
+DAD_MAX_OUT = 1152
+DAD_MAX_SPANS = 32
+DAD_MAX_PACK = 8
+
+
+class DadLayerDesc(ctypes.Structure):
+    _fields_ = [
+        ("A", ctypes.c_void_p), ("AT", ctypes.c_void_p), ("D", ctypes.c_void_p), ("DT", ctypes.c_void_p),
+        ("lda", ctypes.c_longlong), ("ldat", ctypes.c_longlong), ("ldd", ctypes.c_longlong), ("lddt", ctypes.c_longlong),
+        ("N", ctypes.c_int), ("n_in", ctypes.c_int), ("n_out", ctypes.c_int), ("pad_", ctypes.c_int),
+        ("ZN", ctypes.c_void_p), ("ZI", ctypes.c_void_p), ("ZO", ctypes.c_void_p), ("V0", ctypes.c_void_p),
+        ("ldzn", ctypes.c_longlong), ("ldzi", ctypes.c_longlong), ("ldzo", ctypes.c_longlong),
+        ("W", ctypes.c_void_p), ("U", ctypes.c_void_p), ("V", ctypes.c_void_p),
+        ("fact_off", ctypes.c_longlong),
+        ("Uc", ctypes.c_void_p), ("Vc", ctypes.c_void_p),
+        ("G", ctypes.c_void_p), ("ldg", ctypes.c_longlong),
+    ]
+
+
+class DadDesc(ctypes.Structure):
+    _fields_ = [
+        ("layer", DadLayerDesc * DAD_MAX_LAYERS),
+        ("fact", ctypes.c_void_p * MAX_RANKS),
+        ("flags", ctypes.c_void_p * MAX_RANKS),
+        ("slot_floats", ctypes.c_longlong), ("dense_off", ctypes.c_longlong),
+        ("span_off", ctypes.c_longlong * DAD_MAX_SPANS),
+        ("span_len", ctypes.c_int * DAD_MAX_SPANS),
+        ("flat_grad", ctypes.c_void_p),
+        ("dev_state", ctypes.c_void_p),
+        ("grad_scale", ctypes.c_float),
+        ("n_layers", ctypes.c_int), ("mode", ctypes.c_int), ("iters", ctypes.c_int), ("cluster", ctypes.c_int),
+        ("nsplit", ctypes.c_int), ("nranks", ctypes.c_int), ("rank", ctypes.c_int), ("use_flags", ctypes.c_int),
+        ("n_spans", ctypes.c_int), ("rank_cols", ctypes.c_int),
+    ]
+
+
+class DadPackDesc(ctypes.Structure):
+    _fields_ = [
+        ("src", ctypes.c_void_p * DAD_MAX_PACK), ("rows", ctypes.c_void_p * DAD_MAX_PACK),
+        ("colsT", ctypes.c_void_p * DAD_MAX_PACK),
+        ("lds", ctypes.c_longlong * DAD_MAX_PACK), ("ldr", ctypes.c_longlong * DAD_MAX_PACK),
+        ("ldt", ctypes.c_longlong * DAD_MAX_PACK),
+        ("N", ctypes.c_int * DAD_MAX_PACK), ("d", ctypes.c_int * DAD_MAX_PACK),
+        ("count", ctypes.c_int),
+    ]

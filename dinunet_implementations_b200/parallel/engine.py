@@ -90,28 +90,18 @@ class DeviceEngine:
             # both exchange phases are device-side (reduce kernel with device-resident epochs) and all state
             # (error feedback, warm-started Q) is updated in place: the step can be captured
         elif self.agg_engine == "rankDAD":
-            from ..distrib.rankdad import _LinearTap
+            from ..distrib.rankdad import make_taps, CapturedTap
             from .lowrank_fused import DeviceRankDAD
-            from .lowrank_fused import CapturedTap
-            taps, covered = [], set()
-            for m in trainer.nn.values():
-                fused_capture = bool(getattr(m, "fused", False)) and hasattr(m, "dad_capture_keys")
-                if fused_capture:
-                    m._dad_capture = True    # the fused backward hands over (delta, activation) pairs
-                elif hasattr(m, "fused"):
-                    m.fused = False          # otherwise capture on the eager nn.Linear calls
-                for name, mod in m.named_modules():
-                    if isinstance(mod, torch.nn.Linear) and mod.weight.requires_grad:
-                        taps.append(CapturedTap(mod, m, name) if fused_capture else _LinearTap(mod))
-                        covered.add(id(mod.weight))
-                        if mod.bias is not None:
-                            covered.add(id(mod.bias))
+            # device mode reconstructs the weights only; every bias travels dense (exact, a few KB)
+            taps, _ = make_taps(trainer.nn.values())
+            covered = {id(t.module.weight) for t in taps}
             dense = [p for p in self.params if id(p) not in covered]
             self.fused = DeviceRankDAD(group, [self.params], [taps], [dense],
                                        rank=int(self.cache.get("dad_reduction_rank", 10)),
                                        num_pow_iters=int(self.cache.get("dad_num_pow_iters", 5)),
                                        tol=float(self.cache.get("dad_tol", 1e-3)), lr=lr_, optimizer=opt, momentum=mom,
-                                       seed=int(self.cache.get("seed", 0)))
+                                       seed=int(self.cache.get("seed", 0)),
+                                       nsplit=1 if str(self.cache.get("precision_bits", "32")) == "16" else 3)
             # the device rankDAD step has no host syncs and no per-step host state (fixed iteration count,
             # cached seeded start matrices, device-resident exchange epochs): it can live in a CUDA graph
             # when every tapped Linear hands its pair over from the fused backward (module hooks cannot)

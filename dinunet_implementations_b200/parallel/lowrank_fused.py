@@ -190,126 +190,230 @@ class DevicePowerSGD:
             self.opt[li].step()
 
 
-class CapturedTap:
-    """Stands in for ``distrib.rankdad._LinearTap`` when the fused kernels hand over the
-    (delta, activation) pair of a Linear directly (``model._dad_pairs[key]``), so no module hooks
-    and no eager forward are needed."""
+from ..distrib.rankdad import CapturedTap, _LinearTap  # noqa: E402,F401  (re-exported: engine.py, tests)
 
-    def __init__(self, module: torch.nn.Linear, model: torch.nn.Module, key: str):
-        self.module, self.model, self.key = module, model, key
 
-    def pop(self):
-        pairs = getattr(self.model, "_dad_pairs", None) or {}
-        if self.key not in pairs:
-            return None, None
-        D, A = pairs.pop(self.key)
-        D, A = D.float(), A.float()
-        if self.module.bias is not None:
-            A = torch.cat([A, torch.ones(A.shape[0], 1, device=A.device)], 1)
-        return D, A
+def _hilo_rows(x16: torch.Tensor, ld: int):
+    """fp32 ``[16, n]`` → bf16 ``[32, ld]``: rows 0-15 the bf16 roundings, rows 16-31 the bf16 remainders."""
+    n = x16.shape[1]
+    out = torch.zeros(32, ld, device=x16.device, dtype=torch.bfloat16)
+    hi = x16.to(torch.bfloat16)
+    out[:16, :n] = hi
+    out[16:, :n] = (x16 - hi.float()).to(torch.bfloat16)
+    return out
+
+
+class _DadWorkspace:
+    """Persistent buffers of one layer for one of the two rankDAD kernels (``csrc/dad.cu``)."""
+
+    def __init__(self, dev, N, n_in, n_out, rank, seed, stacked=False):
+        f32 = dict(device=dev, dtype=torch.float32)
+        b16 = dict(device=dev, dtype=torch.bfloat16)
+        self.N, self.n_in, self.n_out = int(N), int(n_in), int(n_out)
+        self.ZN = torch.zeros(32, _r8(N), **b16)
+        self.ZI = torch.zeros(32, _r8(n_in), **b16)
+        self.ZO = torch.zeros(32, _r8(n_out), **b16)
+        v0 = torch.zeros(native.DAD_R, n_in, **f32)
+        v0[:rank] = lowrank._seeded_normal((n_in, rank), seed, dev, torch.float32).t()
+        self.V0 = _hilo_rows(v0, _r8(n_in))
+        self.W = torch.zeros(n_out, native.DAD_R, **f32)
+        self.U = torch.zeros(n_out, native.DAD_R, **f32)
+        self.V = torch.zeros(n_in, native.DAD_R, **f32)
+        if stacked:       # mode 1: the kernel builds its own operands from the received factors
+            self.A = torch.zeros(N, _r8(n_in), **b16)
+            self.AT = torch.zeros(n_in, _r8(N), **b16)
+            self.D = torch.zeros(N, _r8(n_out), **b16)
+            self.DT = torch.zeros(n_out, _r8(N), **b16)
+            self.Uc = torch.zeros(n_out, 64, **b16)
+            self.Vc = torch.zeros(n_in, 64, **b16)
+
+    def fill(self, L: "native.DadLayerDesc"):
+        L.N, L.n_in, L.n_out = self.N, self.n_in, self.n_out
+        L.ZN, L.ZI, L.ZO, L.V0 = self.ZN.data_ptr(), self.ZI.data_ptr(), self.ZO.data_ptr(), self.V0.data_ptr()
+        L.ldzn, L.ldzi, L.ldzo = self.ZN.stride(0), self.ZI.stride(0), self.ZO.stride(0)
+        L.W, L.U, L.V = self.W.data_ptr(), self.U.data_ptr(), self.V.data_ptr()
+
+
+def _tma_ok(t):
+    return (t is not None and t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1
+            and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0)
+
+
+def dad_kernels_supported(dims, rank):
+    """The rankDAD kernels keep one row block of the left factor in registers while orthogonalising:
+    ``out <= DAD_MAX_OUT`` per layer; at most ``DAD_MAX_LAYERS`` layers per launch group is handled by
+    splitting into several launches, so only the width and the rank bound the envelope."""
+    return rank <= native.DAD_R and all(o <= native.DAD_MAX_OUT for o, _ in dims)
 
 
 class DeviceRankDAD:
-    """rankDAD across sites.  ``taps[s]`` = list of ``distrib.rankdad._LinearTap`` of site s (same
-    order on every site); ``dense[s]`` = parameters not covered by a tapped Linear."""
+    """rankDAD across sites on the device kernels of ``csrc/dad.cu``.
+
+    ``taps[s]``: the taps (``_LinearTap`` / ``CapturedTap``) of site s, same order on every site; ``dense[s]``:
+    the parameters not reconstructed from factors (norm layers and, in device mode, every bias: the bias
+    gradient ``Σ_rows Δ`` is exact and tiny, so it travels dense instead of as an extra activation column).
+    Per step and site: [one pack launch for pairs that arrive in fp32] → compress kernel (all layers; its tail
+    is the factor all-gather) → recompress + reconstruct kernel (writes ``W.grad`` into the flat gradient
+    buffer) → fused Adam/SGD.  ``dad_tol`` is not evaluated: all ``num_pow_iters`` iterations run (no host sync).
+    """
 
     def __init__(self, group: SiteGroup, site_params, taps, dense, rank=10, num_pow_iters=5, tol=1e-3, lr=1e-3,
-                 optimizer="adam", momentum=0.0, seed=0):
+                 optimizer="adam", momentum=0.0, seed=0, nsplit=3, cluster=None):
         self.group = group
         self.sites = list(range(group.nsites)) if group.backend == "local" else [group.rank]
         self.S = group.nsites
         self.rank, self.iters, self.tol, self.seed = int(rank), int(num_pow_iters), float(tol), int(seed)
+        self.nsplit = int(nsplit)
+        self.cluster = int(cluster or os.environ.get("DINUNET_DAD_CLUSTER", "8"))
         dev = group.device
         self.opt = [_LocalOptim(dev, ps, lr, optimizer, momentum) for ps in site_params]
         self.taps, self.dense = taps, dense
         t0 = taps[0]
-        self.dims = [(t.module.weight.shape[0], t.module.weight.shape[1] + (1 if t.module.bias is not None else 0))
-                     for t in t0]
-        r = self.rank
-        # one slot per site: [d_0 (r x out), a_0 (r x in), d_1, ...]; dense grads are averaged separately
+        self.dims = [(t.module.weight.shape[0], t.module.weight.shape[1]) for t in t0]
+        if not dad_kernels_supported(self.dims, self.rank):
+            raise ValueError(f"rankDAD device kernels need out <= {native.DAD_MAX_OUT} per Linear and rank <= "
+                             f"{native.DAD_R}; got dims {self.dims}, rank {self.rank}")
+        R = native.DAD_R
+        # slot layout (floats): per layer U [out,16] then V [in,16]; then the dense gradients
         self.f_off, cur = [], 0
         for (o, i) in self.dims:
-            self.f_off.append((cur, cur + _r8(r * o)))
-            cur += _r8(r * o) + _r8(r * i)
-        self.slot = cur
-        self.xf = _Exchange(group, self.slot * self.S, "dad_factors")
-        n_dense = sum(p.numel() for p in dense[0])
-        self.xd = _Exchange(group, max(n_dense, 8), "dad_dense") if n_dense else None
+            self.f_off.append(cur)
+            cur += (o + i) * R
+        self.dense_off = cur
+        self.spans = []
+        for li in range(len(self.sites)):
+            pid = {id(p): k for k, p in enumerate(site_params[li])}
+            sp = [(self.opt[li].offs[pid[id(p)]], p.numel()) for p in dense[li]]
+            self.spans.append(sp)
+        if len(self.spans[0]) > native.DAD_MAX_SPANS:
+            raise ValueError(f"rankDAD device kernels take at most {native.DAD_MAX_SPANS} dense parameters")
+        cur += sum(n for _, n in self.spans[0])
+        self.slot = (cur + 3) // 4 * 4
+        self.fact = group.alloc("dad.fact", 2 * self.S * self.slot, torch.float32)
+        self.flags = group.alloc("dad.flags", 64, torch.int32)
+        self.state = [torch.zeros(4, device=dev, dtype=torch.int32) for _ in self.sites]
+        self.ws0 = [dict() for _ in self.sites]          # (layer, N) -> _DadWorkspace, compress
+        n1 = self.nsplit * self.S * R
+        self.ws1 = [[_DadWorkspace(dev, n1, i, o, self.rank, self.seed + 101 * k, stacked=True)
+                     for k, (o, i) in enumerate(self.dims)] for _ in self.sites]
+        self._pack_bufs = [dict() for _ in self.sites]
+        self._desc1 = [None for _ in self.sites]
+        self.groups = [list(range(a, min(a + native.DAD_MAX_LAYERS, len(self.dims))))
+                       for a in range(0, len(self.dims), native.DAD_MAX_LAYERS)]
 
     def zero_grad(self, site=None):
         for li, s in enumerate(self.sites):
             if site is None or s == site:
                 self.opt[li].flat_grad.zero_()
 
-    # The layers are independent of one another and each one's subspace iteration is a strictly serial chain
-    # of tiny kernels (a few SMs each), so the per-layer work is spread over side streams: concurrent in
-    # eager mode, parallel branches when the step is captured in a CUDA graph.
-    _N_STREAMS = int(os.environ.get("DINUNET_DAD_STREAMS", "8"))
+    # ------------------------------------------------------------------ operands
+    def _operands(self, li, k, entries, packs):
+        """bf16 (D, DT, A, AT) of layer k; blocks that arrive without both orientations (or in fp32) are queued
+        for the pack kernel into persistent buffers."""
+        o, i = self.dims[k]
+        if len(entries) > 1:        # local_iterations > 1: stack the micro-batches along N
+            ent = {"D": torch.cat([e["D"].float() for e in entries], 0), "A": torch.cat([e["A"].float() for e in entries], 0)}
+        else:
+            ent = entries[0]
+        out = {}
+        N = ent["D"].shape[0]
+        for key, tkey, width in (("D", "DT", o), ("A", "AT", i)):
+            x, xt = ent[key], ent.get(tkey)
+            if _tma_ok(x) and _tma_ok(xt):
+                out[key], out[tkey] = x, xt
+                continue
+            bufs = self._pack_bufs[li]
+            bk = (k, key, N)
+            if bk not in bufs:
+                bufs[bk] = (torch.zeros(N, _r8(width), device=x.device, dtype=torch.bfloat16),
+                            torch.zeros(width, _r8(N), device=x.device, dtype=torch.bfloat16))
+            rows, colsT = bufs[bk]
+            src = x if (x.dtype == torch.float32 and x.stride(1) == 1) else x.float().contiguous()
+            packs.append((src, rows, colsT, N, width))
+            out[key], out[tkey] = rows[:, :width], colsT[:, :N]
+        return out, N
 
-    def _streams(self):
-        if getattr(self, "_side", None) is None:
-            self._side = [torch.cuda.Stream(device=self.group.device) for _ in range(self._N_STREAMS)]
-        return self._side
+    def _run_packs(self, packs):
+        lib = native.require_gpu()
+        for a in range(0, len(packs), native.DAD_MAX_PACK):
+            d = native.DadPackDesc()
+            chunk = packs[a:a + native.DAD_MAX_PACK]
+            for j, (src, rows, colsT, N, width) in enumerate(chunk):
+                d.src[j], d.rows[j], d.colsT[j] = src.data_ptr(), rows.data_ptr(), colsT.data_ptr()
+                d.lds[j], d.ldr[j], d.ldt[j] = src.stride(0), rows.stride(0), colsT.stride(0)
+                d.N[j], d.d[j] = N, width
+            d.count = len(chunk)
+            self._keep = getattr(self, "_keep", [])
+            self._keep.append([p[0] for p in chunk])      # sources stay alive until the launch has been queued
+            native.check(lib.dnb_dad_pack(ctypes.byref(d), native.stream()), "dnb_dad_pack")
+        self._keep = []
 
-    def _fork(self):
-        main = torch.cuda.current_stream(self.group.device)
-        side = self._streams()
-        for st in side:
-            st.wait_stream(main)
-        return main, side
+    def _common(self, d, li, s, mode):
+        g = self.group
+        fp, gp = g.ptrs("dad.fact"), g.ptrs("dad.flags")
+        for r in range(g.nsites):
+            d.fact[r], d.flags[r] = fp[r], gp[r]
+        d.slot_floats, d.dense_off = self.slot, self.dense_off
+        for j, (off, n) in enumerate(self.spans[li]):
+            d.span_off[j], d.span_len[j] = off, n
+        d.n_spans = len(self.spans[li])
+        d.flat_grad = self.opt[li].flat_grad.data_ptr()
+        d.dev_state = self.state[li].data_ptr()
+        d.grad_scale = 1.0 / self.S
+        d.mode, d.iters, d.cluster, d.nsplit = mode, self.iters, self.cluster, self.nsplit
+        d.nranks, d.rank, d.use_flags, d.rank_cols = g.nsites, s, int(g.use_flags), self.rank
 
-    @staticmethod
-    def _join(main, side):
-        for st in side:
-            main.wait_stream(st)
+    def _launch_groups(self, build, li, s, mode):
+        """One launch for the model's tapped layers (``step`` refuses models with more than DAD_MAX_LAYERS)."""
+        lib = native.require_gpu()
+        for gi, layers in enumerate(self.groups):
+            d = native.DadDesc()
+            self._common(d, li, s, mode)
+            for j, k in enumerate(layers):
+                build(d.layer[j], k)
+            d.n_layers = len(layers)
+            if gi != 0:
+                d.n_spans = 0
+            native.check(lib.dnb_dad_step(ctypes.byref(d), native.stream()), f"dnb_dad_step(mode {mode})")
 
     def step(self):
-        r = self.rank
+        if len(self.groups) > 1:
+            raise NotImplementedError(f"more than {native.DAD_MAX_LAYERS} tapped Linear layers per model")
+        R = native.DAD_R
+        held = []
         for li, s in enumerate(self.sites):
-            pay = self.xf.payload[s]
-            pay.zero_()                                           # other sites' slots must stay zero
-            base = s * self.slot
-            pairs = [tap.pop() for tap in self.taps[li]]          # on the stream that produced them
-            main, side = self._fork()
-            for k, (D, A) in enumerate(pairs):
-                o, i = self.dims[k]
-                with torch.cuda.stream(side[k % len(side)]):
-                    if D is None:
-                        D, A = torch.zeros(1, o, device=pay.device), torch.zeros(1, i, device=pay.device)
-                    d, a, _ = lowrank.dad_compress(D, A, r, self.iters, self.tol, self.seed + k)
-                    od, oa = self.f_off[k]
-                    pay[base + od: base + od + r * o].copy_(d.reshape(-1))
-                    pay[base + oa: base + oa + r * i].copy_(a.reshape(-1))
-            self._join(main, side)
-            if self.xd is not None:
-                flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1)
-                                  for p in self.dense[li]])
-                self.xd.payload[s][:flat.numel()].copy_(flat)
-        Fm = self.xf.mean()                                       # mean of disjoint slots = concat / S
-        Dm = self.xd.mean() if self.xd is not None else None
-        for li, s in enumerate(self.sites):
-            cat = Fm[li] * float(self.S)                          # undo the mean: plain concatenation
-            main, side = self._fork()
+            packs, ops = [], []
             for k, tap in enumerate(self.taps[li]):
+                entries = tap.pop_entries()
+                if not entries:
+                    raise RuntimeError(f"rankDAD: Linear #{k} {self.dims[k]} produced no (delta, activation) pair this "
+                                       "step (is the model's fused path bypassing its hooks?)")
+                ops.append(self._operands(li, k, entries, packs))
+            if packs:
+                self._run_packs(packs)
+            held.append(ops)
+
+            def build0(L, k, li=li, ops=ops):
                 o, i = self.dims[k]
-                od, oa = self.f_off[k]
-                with torch.cuda.stream(side[k % len(side)]):
-                    ds = [cat[q * self.slot + od: q * self.slot + od + r * o].view(r, o) for q in range(self.S)]
-                    as_ = [cat[q * self.slot + oa: q * self.slot + oa + r * i].view(r, i) for q in range(self.S)]
-                    d, a, _ = lowrank.dad_reduce(ds, as_, r, self.iters, self.tol, self.seed + 101 * k, average=True)
-                    # reconstruction GEMM  G[out, in] = d^T a  (K = r)
-                    w = tap.module.weight
-                    G = torch.empty(o, i, device=w.device)
-                    gemm_bf16(_bf16_pad_cols(d.t().contiguous()), _bf16_pad_cols(a.t().contiguous()), out=G)
-                    if tap.module.bias is not None:
-                        tap.module.bias.grad.copy_(G[:, -1])
-                        w.grad.copy_(G[:, :-1])
-                    else:
-                        w.grad.copy_(G)
-            self._join(main, side)
-            if Dm is not None:
-                off = 0
-                for p in self.dense[li]:
-                    p.grad.copy_(Dm[li][off:off + p.numel()].view_as(p))
-                    off += p.numel()
+                t, N = ops[k]
+                ws = self.ws0[li].get((k, N))
+                if ws is None:
+                    ws = self.ws0[li][(k, N)] = _DadWorkspace(self.group.device, N, i, o, self.rank, self.seed + k)
+                ws.fill(L)
+                L.A, L.AT, L.D, L.DT = t["A"].data_ptr(), t["AT"].data_ptr(), t["D"].data_ptr(), t["DT"].data_ptr()
+                L.lda, L.ldat, L.ldd, L.lddt = t["A"].stride(0), t["AT"].stride(0), t["D"].stride(0), t["DT"].stride(0)
+                L.fact_off = self.f_off[k]
+            self._launch_groups(build0, li, s, 0)
+        for li, s in enumerate(self.sites):
+            def build1(L, k, li=li):
+                ws = self.ws1[li][k]
+                ws.fill(L)
+                L.A, L.AT, L.D, L.DT = ws.A.data_ptr(), ws.AT.data_ptr(), ws.D.data_ptr(), ws.DT.data_ptr()
+                L.lda, L.ldat, L.ldd, L.lddt = ws.A.stride(0), ws.AT.stride(0), ws.D.stride(0), ws.DT.stride(0)
+                L.fact_off = self.f_off[k]
+                L.Uc, L.Vc = ws.Uc.data_ptr(), ws.Vc.data_ptr()
+                w = self.taps[li][k].module.weight
+                L.G, L.ldg = w.grad.data_ptr(), w.shape[1]
+            self._launch_groups(build1, li, s, 1)
             self.opt[li].step()
+        self._held = held          # operand tensors of this step stay referenced until the next one

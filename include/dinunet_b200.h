@@ -209,6 +209,7 @@ typedef struct DnbHeadBwdDesc {
     float* dz1;                /* [B,N1] scratch handed from the first to the second backward launch */
     int training, accumulate;
     int B, N0, N1, N2, N3;
+    float* dz2;                /* optional [B,N2] out: gradient at the second layer's pre-activation (rankDAD pairs) */
 } DnbHeadBwdDesc;
 int dnb_head_backward(const DnbHeadBwdDesc* desc, void* stream);
 

@@ -78,9 +78,9 @@ def test_device_rankdad_equals_dsgd_when_rank_covers_batch():
     nets = _nets(S, seed=2)
     params = [[p for p in n.parameters()] for n in nets]
     taps = [[_LinearTap(m) for m in n.modules() if isinstance(m, torch.nn.Linear)] for n in nets]
-    dense = [[p for m in n.modules() if isinstance(m, torch.nn.BatchNorm1d) for p in m.parameters()] for n in nets]
+    dense = [[p for p in n.parameters() if p.dim() < 2] for n in nets]       # norm layers and biases travel dense
     g = SiteGroup.local(S, 8 << 20)
-    eng = DeviceRankDAD(g, params, taps, dense, rank=16, num_pow_iters=40, tol=0.0, lr=0.1, optimizer="sgd")
+    eng = DeviceRankDAD(g, params, taps, dense, rank=16, num_pow_iters=8, tol=0.0, lr=0.1, optimizer="sgd")
     w0 = [p.detach().clone() for p in params[0]]
     xs = [torch.randn(B, 40, device="cuda") for _ in range(S)]
     ys = [torch.randint(0, 3, (B,), device="cuda") for _ in range(S)]
@@ -95,9 +95,91 @@ def test_device_rankdad_equals_dsgd_when_rank_covers_batch():
         mean_g = torch.stack([grads[s][i] for s in range(S)]).mean(0)
         expect = w0[i] - 0.1 * mean_g
         scale = max((0.1 * mean_g).abs().max().item(), 1e-6)
-        assert torch.allclose(p.detach(), expect, atol=0.05 * scale + 1e-6), (i, (p - expect).abs().max(), scale)
+        assert torch.allclose(p.detach(), expect, atol=0.02 * scale + 1e-6), (i, (p - expect).abs().max(), scale)
     for a, b in zip(params[0], params[1]):
         assert torch.equal(a, b)
+    g.close()
+
+
+def _bf16(x):
+    return x.to(torch.bfloat16).float()
+
+
+@pytest.mark.parametrize("N,n_in,n_out,S", [(1568, 256, 768, 2), (1568, 1000, 256, 3), (16, 384, 256, 4), (300, 66, 40, 8)])
+def test_dad_kernels_match_fp64_oracle(N, n_in, n_out, S):
+    """K2a + K2b (csrc/dad.cu) against the fp64 restatement of the same algorithm (distrib/lowrank.py): per-site
+    rank-10 subspace iteration, stacking, re-compression, reconstruction.  The oracle gets the same bf16-rounded
+    (delta, activation) inputs and the same seeded start matrices; what remains is the kernels' hi/lo bf16 iterates."""
+    from dinunet_implementations_b200.distrib import lowrank
+    from dinunet_implementations_b200.distrib.rankdad import _LinearTap
+    from dinunet_implementations_b200.parallel.comm import SiteGroup
+    from dinunet_implementations_b200.parallel.lowrank_fused import DeviceRankDAD
+    torch.manual_seed(N + n_in)
+    r, iters, seed = 10, 5, 3
+    lins = [torch.nn.Linear(n_in, n_out, bias=False).cuda() for _ in range(S)]
+    for l in lins[1:]:
+        l.load_state_dict(lins[0].state_dict())
+    params = [[l.weight] for l in lins]
+    taps = [[_LinearTap(l)] for l in lins]
+    g = SiteGroup.local(S, 64 << 20)
+    eng = DeviceRankDAD(g, params, taps, [[] for _ in lins], rank=r, num_pow_iters=iters, tol=0.0, lr=1.0, optimizer="sgd", seed=seed)
+    w0 = lins[0].weight.detach().clone()
+    # activations with a decaying spectrum (a few dominant directions, like real gradients) so that rank 10 means something
+    basis = torch.randn(24, n_in, device="cuda")
+    As = [_bf16((torch.randn(N, 24, device="cuda") * torch.logspace(0, -2, 24, device="cuda")) @ basis) for _ in range(S)]
+    Ds = [_bf16(torch.randn(N, n_out, device="cuda") * 0.1) for _ in range(S)]
+    eng.zero_grad()
+    for s in range(S):
+        lins[s].train()
+        (lins[s](As[s]) * Ds[s]).sum().backward()          # delta = Ds[s] exactly
+    eng.step()
+    torch.cuda.synchronize()
+    G_dev = (w0 - lins[0].weight.detach()).double()
+    ds, as_ = [], []
+    for s in range(S):
+        d, a, _ = lowrank.dad_compress(Ds[s].double(), As[s].double(), r, iters, 0.0, seed + 0)
+        ds.append(d); as_.append(a)
+    d, a, _ = lowrank.dad_reduce(ds, as_, r, iters, 0.0, seed + 0, average=True)
+    G_ref = lowrank.dad_reconstruct(d, a)
+    G_true = sum(D.double().t() @ A.double() for D, A in zip(Ds, As)) / S
+    err = ((G_dev - G_ref).norm() / G_ref.norm()).item()
+    base = ((G_ref - G_true).norm() / G_true.norm()).item()       # what rank 10 itself loses
+    assert err < 0.02, (err, base)
+    assert ((G_dev - G_true).norm() / G_true.norm()).item() < base + 0.02
+    for s in range(1, S):
+        assert torch.equal(lins[0].weight, lins[s].weight)        # every site reconstructs the same bits
+    g.close()
+
+
+def test_dad_kernels_exact_for_low_rank_gradients():
+    """rank(G) <= r on every site and in the sum: the compressed exchange loses nothing."""
+    from dinunet_implementations_b200.distrib.rankdad import _LinearTap
+    from dinunet_implementations_b200.parallel.comm import SiteGroup
+    from dinunet_implementations_b200.parallel.lowrank_fused import DeviceRankDAD
+    torch.manual_seed(7)
+    S, N, n_in, n_out, r = 2, 512, 192, 320, 10
+    lins = [torch.nn.Linear(n_in, n_out, bias=False).cuda() for _ in range(S)]
+    for l in lins[1:]:
+        l.load_state_dict(lins[0].state_dict())
+    taps = [[_LinearTap(l)] for l in lins]
+    g = SiteGroup.local(S, 32 << 20)
+    eng = DeviceRankDAD(g, [[l.weight] for l in lins], taps, [[] for _ in lins], rank=r, num_pow_iters=5, lr=1.0, optimizer="sgd")
+    w0 = lins[0].weight.detach().clone()
+    # every site's activations live in the same 5-dimensional subspace: rank(sum_s D_s^T A_s) <= 5
+    basis = _bf16(torch.randn(5, n_in, device="cuda"))
+    As = [_bf16(torch.randint(-2, 3, (N, 5), device="cuda").float()) @ basis for _ in range(S)]
+    As = [_bf16(a) for a in As]
+    Ds = [_bf16(torch.randn(N, n_out, device="cuda")) for _ in range(S)]
+    eng.zero_grad()
+    for s in range(S):
+        lins[s].train()
+        (lins[s](As[s]) * Ds[s]).sum().backward()
+    eng.step()
+    torch.cuda.synchronize()
+    G_dev = (w0 - lins[0].weight.detach()).double()
+    G_true = sum(D.double().t() @ A.double() for D, A in zip(Ds, As)) / S
+    rel = ((G_dev - G_true).norm() / G_true.norm()).item()
+    assert rel < 5e-3, rel
     g.close()
 
 
@@ -159,7 +241,11 @@ def test_fused_capture_pairs_reproduce_the_weight_gradients():
     torch.cuda.synchronize()
     mods_a = dict(a.named_modules())
     assert set(b._dad_pairs) == set(b.dad_capture_keys())
-    for key, (D, A) in b._dad_pairs.items():
+    for key, entries in b._dad_pairs.items():
+        assert len(entries) == 1
+        D, A = entries[0]["D"], entries[0]["A"]
+        if "DT" in entries[0]:      # both orientations are handed over for the TMA-fed rankDAD kernels
+            assert torch.equal(entries[0]["DT"].float(), D.float().t()) and torch.equal(entries[0]["AT"].float(), A.float().t())
         G = D.float().t() @ A.float()
         ref = mods_a[key].weight.grad
         s = max(ref.abs().max().item(), 1e-6)
