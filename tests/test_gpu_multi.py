@@ -38,3 +38,13 @@ def test_device_federation_across_gpus(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count(": OK") == 3, r.stdout[-2000:]
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_lowrank_engines_across_gpus():
+    n = min(torch.cuda.device_count(), 4)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", _free_port(), os.path.join(ROOT, "tests/multigpu/mp_lowrank_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "DeviceEngine rankDAD multi-site: OK" in r.stdout and "DeviceEngine powerSGD multi-site: OK" in r.stdout
