@@ -71,6 +71,10 @@ class FusedDSGD:
         self.params = group.alloc(f"{name}.params", self.n, torch.float32)
         self.grads = group.alloc(f"{name}.grads", self.n, wire_dtype)
         self.shadow = group.alloc(f"{name}.shadow", self.n, torch.bfloat16) if shadow_bf16 else None
+        # every instance owns its signal pad: two reducers that shared one would see each other's barrier
+        # generations and run ahead of their peers (their epochs advance independently)
+        self._flag_name = f"{name}.flags"
+        group.alloc(self._flag_name, native.SIGNAL_WORDS, torch.int32)
         self._names = (f"{name}.params", f"{name}.grads", f"{name}.shadow" if shadow_bf16 else None)
         dev = group.device
         n_states = group.nsites if group.backend == "local" else 1
@@ -172,7 +176,7 @@ class FusedDSGD:
         g = self.group
         gp, pp = g.ptrs(self._names[1]), g.ptrs(self._names[0])
         sp = g.ptrs(self._names[2]) if self._names[2] else [0] * g.nsites
-        fp = g.ptrs("__flags__")
+        fp = g.ptrs(self._flag_name)
         for r in range(g.nsites):
             d.grads[r], d.params[r], d.shadow_bf16[r], d.flags[r] = gp[r], pp[r], sp[r] or None, fp[r]
         d.m, d.v = self.m[state_ix].data_ptr(), self.v[state_ix].data_ptr()
