@@ -128,6 +128,7 @@ class DeviceEngine:
         self.use_graph = bool(use_graph)
         self.graph_warmup = int(graph_warmup)
         self._graph = None
+        self.graph_replays = 0           # counted, not derived: bench.py reports launches from it
         self.kernels_per_step = None
         self._static_in = None
         self._static_out = None
@@ -230,10 +231,12 @@ class DeviceEngine:
         if self.use_graph and self._graph is None and self.steps > self.graph_warmup:
             if self._capture(dev_batch):
                 self._graph.replay()      # capture records but does not execute: run the captured step once
+                self.graph_replays += 1
                 return self._static_out
         if self._graph is not None:
             self._load_static(dev_batch)
             self._graph.replay()
+            self.graph_replays += 1
             return self._static_out
         return self._step_body(dev_batch)
 
@@ -335,6 +338,7 @@ class DeviceEngine:
             copy(fs["static_ptr"][k], buf[k].data_ptr(), fs["nbytes"][k], 3, cur_h)
         fs["consumed"][slot].record(cur)                   # staging slot free again once these copies have run
         self._graph.replay()
+        self.graph_replays += 1
         fs["used"][slot] = True
         fs.setdefault("host_ref", [None, None])[slot] = host_batch   # keep the pinned source alive while its DMA may run
         ring_ix = len(self._pending) % 64
