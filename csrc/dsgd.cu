@@ -47,7 +47,51 @@ struct DsgdArgs {
     uint32_t* dev_state;   // optional {completed steps, blocks-done counter, lr bits}: makes the launch replayable
     float* stage;          // optional fp32 local gradients to cast into grads[rank] in-kernel (16-bit wire)
     int zero_stage;
+    // mode 2 (NVLS): multicast addresses of the same symmetric buffers.  A load through grads_mc is reduced over all
+    // sites inside the NVSwitch, a store through params_mc / shadow_mc lands on every site.
+    const void* grads_mc;
+    float* params_mc;
+    __nv_bfloat16* shadow_mc;
 };
+
+// ---- NVLS (multimem) primitives: 16 bytes per instruction -------------------------------------------------
+template <int WIRE>
+__device__ __forceinline__ void mc_load_reduce8(const void* mc_base, long long i, float (&x)[8]) {
+    if constexpr (WIRE == 0) {
+        const float* p = reinterpret_cast<const float*>(mc_base) + i;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "l"(p) : "memory");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x[4]), "=f"(x[5]), "=f"(x[6]), "=f"(x[7]) : "l"(p + 4) : "memory");
+    } else {
+        const uint16_t* p = reinterpret_cast<const uint16_t*>(mc_base) + i;
+        uint32_t w[4];
+        if constexpr (WIRE == 1)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
+        else
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if constexpr (WIRE == 1) {
+                x[2 * k] = __uint_as_float(w[k] << 16);
+                x[2 * k + 1] = __uint_as_float(w[k] & 0xFFFF0000u);
+            } else {
+                __half2 h = *reinterpret_cast<const __half2*>(&w[k]);
+                float2 f = __half22float2(h);
+                x[2 * k] = f.x;
+                x[2 * k + 1] = f.y;
+            }
+        }
+    }
+}
+__device__ __forceinline__ void mc_store16(void* mc_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc_addr), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)), "f"(__uint_as_float(c)),
+                 "f"(__uint_as_float(d))
+                 : "memory");
+}
 
 __device__ __forceinline__ void flag_barrier(const DsgdArgs& a, int phase, uint32_t epoch) {
     // Every block pairs up with the same-index block on each peer.
@@ -115,8 +159,11 @@ __device__ __forceinline__ void store8_f32(float* base, long long i, const float
     p[1] = make_float4(x[4], x[5], x[6], x[7]);
 }
 
-template <int WIRE>
+// NR = number of sites as a compile-time constant (1, 2, 4, 8: the peer loop unrolls exactly and the staging
+// registers are sized for it) or 0 = run-time count (any 1..8, guarded loop).
+template <int WIRE, int NR>
 __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs a) {
+    const int nranks = NR > 0 ? NR : a.nranks;
     // Step-dependent scalars come either from the launch arguments or — when the launch lives in a
     // CUDA graph and is replayed unchanged — from a small device-resident state block.
     dnb::pdl_wait();
@@ -138,8 +185,8 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
             // loop below), so the per-block flag barrier is all the ordering the peers need; the local reduce
             // re-reads only what the same thread wrote.
             void* wire = const_cast<void*>(a.grads[a.rank]);
-            const int shards = (a.mode == 0 && a.nranks > 1) ? a.nranks : 1;
-            const long long per = shards > 1 ? ((a.n / 8 + a.nranks - 1) / a.nranks) * 8 : a.n;
+            const int shards = (a.mode != 1 && nranks > 1) ? nranks : 1;
+            const long long per = shards > 1 ? ((a.n / 8 + nranks - 1) / nranks) * 8 : a.n;
             for (int p = 0; p < shards; ++p) {
                 long long plo = per * p, phi = plo + per < a.n ? plo + per : a.n;
                 if (plo > phi) plo = phi;
@@ -158,25 +205,37 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
     if (a.use_flags) flag_barrier(a, 0, epoch);
 
     long long lo = 0, hi = a.n;
-    if (a.mode == 0 && a.nranks > 1) {
-        long long per = ((a.n / 8 + a.nranks - 1) / a.nranks) * 8;
+    if (a.mode != 1 && nranks > 1) {
+        long long per = ((a.n / 8 + nranks - 1) / nranks) * 8;
         lo = per * a.rank;
         hi = lo + per < a.n ? lo + per : a.n;
         if (lo > hi) lo = hi;
     }
     for (long long i = lo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < hi; i += stride) {
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        // all peers' loads are issued before the first add: nranks 16-byte requests in flight
-        float x[kMaxRanks][8];
+        if (a.mode == 2) {
+            // one instruction pair: the switch returns the sum over all sites
+            mc_load_reduce8<WIRE>(a.grads_mc, i, g);
+        } else {
+            // the loads of (up to) four peers are issued before the first add: 4 x 16-byte requests in flight per
+            // thread, and the staging registers stay at 32 whatever the site count (the fixed summation order
+            // 0,1,2,.. is the same on every site)
+            constexpr int kChunk = 4;
+            constexpr int kTop = NR > 0 ? NR : kMaxRanks;
 #pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r)
-            if (r < a.nranks) load8<WIRE>(a.grads[r], i, x[r]);
+            for (int r0 = 0; r0 < kTop; r0 += kChunk) {
+                float x[kChunk][8];
 #pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r)
-            if (r < a.nranks) {
+                for (int r = 0; r < kChunk; ++r)
+                    if (r0 + r < kTop && (NR > 0 || r0 + r < nranks)) load8<WIRE>(a.grads[r0 + r], i, x[r]);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) g[k] += x[r][k];
+                for (int r = 0; r < kChunk; ++r)
+                    if (r0 + r < kTop && (NR > 0 || r0 + r < nranks)) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) g[k] += x[r][k];
+                    }
             }
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) g[k] *= a.grad_scale;
 
@@ -219,10 +278,16 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
         sh.y = dnb::pack_bf16x2(p[2], p[3]);
         sh.z = dnb::pack_bf16x2(p[4], p[5]);
         sh.w = dnb::pack_bf16x2(p[6], p[7]);
-        if (a.mode == 0) {
+        if (a.mode == 2) {
+            // one multicast store reaches every site's copy (this one included)
+            mc_store16(a.params_mc + i, __float_as_uint(p[0]), __float_as_uint(p[1]), __float_as_uint(p[2]), __float_as_uint(p[3]));
+            mc_store16(a.params_mc + i + 4, __float_as_uint(p[4]), __float_as_uint(p[5]), __float_as_uint(p[6]), __float_as_uint(p[7]));
+            if (a.shadow_mc) mc_store16(a.shadow_mc + i, sh.x, sh.y, sh.z, sh.w);
+        } else if (a.mode == 0) {
+            constexpr int kTop = NR > 0 ? NR : kMaxRanks;
 #pragma unroll
-            for (int r = 0; r < kMaxRanks; ++r)
-                if (r < a.nranks) {
+            for (int r = 0; r < kTop; ++r)
+                if (NR > 0 || r < nranks) {
                     store8_f32(a.params[r], i, p);
                     if (a.shadow[r]) *reinterpret_cast<uint4*>(a.shadow[r] + i) = sh;
                 }
@@ -276,12 +341,20 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     a.grad_scale = d->grad_scale; a.momentum = d->momentum; a.epoch = d->epoch;
     a.dev_state = d->dev_state;
     a.stage = d->stage; a.zero_stage = d->zero_stage;
+    a.grads_mc = d->grads_mc; a.params_mc = d->params_mc; a.shadow_mc = reinterpret_cast<__nv_bfloat16*>(d->shadow_mc);
+    DNB_REQUIRE(d->mode >= 0 && d->mode <= 2, "mode must be 0 (two-shot P2P), 1 (one-shot P2P) or 2 (two-shot NVLS multicast)");
+    if (d->mode == 2) {
+        DNB_REQUIRE(d->opt != 2, "NVLS mode updates parameters; use mode 0/1 for a plain reduction");
+        DNB_REQUIRE(a.grads_mc && a.params_mc, "NVLS mode needs the multicast addresses of the gradient and parameter buffers");
+        DNB_REQUIRE((a.shadow_mc != nullptr) == (a.shadow[d->rank] != nullptr), "NVLS mode: shadow and shadow_mc must be given together");
+        DNB_REQUIRE(d->nranks > 1 && d->use_flags, "NVLS mode is for real multi-GPU groups");
+    }
     DNB_REQUIRE(a.stage == nullptr || d->wire != 0, "in-kernel gradient packing is for the 16-bit wire formats only");
     if (a.use_flags)
         for (int r = 0; r < d->nranks; ++r) DNB_REQUIRE(a.flags[r] != nullptr, "flags[%d] is null", r);
 
     long long span = a.n;
-    if (a.mode == 0 && a.nranks > 1) span = ((a.n / 8 + a.nranks - 1) / a.nranks) * 8;
+    if (a.mode != 1 && a.nranks > 1) span = ((a.n / 8 + a.nranks - 1) / a.nranks) * 8;
     int blocks = dnb_ceil_div(span, (long)kThreads * 8);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -289,11 +362,23 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     if (blocks > sms) blocks = sms;           // one CTA per SM: all CTAs co-resident for the flag barrier
     if (blocks > kMaxBlocks) blocks = kMaxBlocks;
     if (blocks < 1) blocks = 1;
-    switch (d->wire) {
-        case 0: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<0>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
-        case 1: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<1>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
-        default: DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<2>, dim3(blocks), dim3(kThreads), 0, stream, 0, a)); break;
+    const int nr = (d->nranks == 1 || d->nranks == 2 || d->nranks == 4 || d->nranks == 8) ? d->nranks : 0;
+#define DNB_DSGD_LAUNCH(W, N) DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<W, N>, dim3(blocks), dim3(kThreads), 0, stream, 0, a))
+#define DNB_DSGD_WIRE(W)                                  \
+    switch (nr) {                                         \
+        case 1: DNB_DSGD_LAUNCH(W, 1); break;             \
+        case 2: DNB_DSGD_LAUNCH(W, 2); break;             \
+        case 4: DNB_DSGD_LAUNCH(W, 4); break;             \
+        case 8: DNB_DSGD_LAUNCH(W, 8); break;             \
+        default: DNB_DSGD_LAUNCH(W, 0); break;            \
     }
+    switch (d->wire) {
+        case 0: DNB_DSGD_WIRE(0); break;
+        case 1: DNB_DSGD_WIRE(1); break;
+        default: DNB_DSGD_WIRE(2); break;
+    }
+#undef DNB_DSGD_WIRE
+#undef DNB_DSGD_LAUNCH
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;

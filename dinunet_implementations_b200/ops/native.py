@@ -140,6 +140,7 @@ class DsgdDesc(ctypes.Structure):
         ("epoch", ctypes.c_uint32),
         ("dev_state", ctypes.c_void_p),
         ("stage", ctypes.c_void_p), ("zero_stage", ctypes.c_int),
+        ("grads_mc", ctypes.c_void_p), ("params_mc", ctypes.c_void_p), ("shadow_mc", ctypes.c_void_p),
     ]
 
 

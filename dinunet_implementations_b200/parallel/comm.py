@@ -7,6 +7,11 @@
   ``torch.distributed`` (bootstrap only — SURVEY §5.8: "the steady-state aggregation paths issue
   no NCCL call") and opens its peers' arenas, so kernels address remote HBM directly over
   NVLink/NVSwitch.
+* **symm** – same process layout, but the arena comes from ``torch.distributed._symmetric_memory`` (CUDA VMM
+  allocation + handle exchange, bootstrap only): besides the per-peer mappings it yields an **NVLS multicast**
+  address of the arena (``mc_base``), through which the aggregation kernels reduce inside the NVSwitch
+  (``multimem.ld_reduce``) and publish with one store for all sites (``multimem.st``).  Chosen automatically when the
+  box supports it (``DINUNET_ARENA=ipc`` forces the plain IPC arena); the kernels themselves never call NCCL.
 * **local** – S simulated sites inside one process on one GPU: S arenas in the same address
   space.  The kernels are identical; only the cross-GPU flag barrier is switched off, because
   kernels that wait for one another must not be launched back-to-back on one device.  This is
@@ -17,6 +22,7 @@ The arena is carved by name (``alloc``) in the same order on every rank, so offs
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -44,6 +50,8 @@ class SiteGroup:
         self._cursor = 0
         self._layout = {}
         self.epoch = 0
+        self.mc_base = 0                       # multicast (NVLS) address of the arena, 0 = not available
+        self._symm = None                      # (tensor, handle) keeping a symmetric-memory arena alive
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -66,6 +74,10 @@ class SiteGroup:
         lib = native.require_gpu()
         rank, world = dist.get_rank(), dist.get_world_size()
         device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        if world > 1 and os.environ.get("DINUNET_ARENA", "symm") != "ipc":
+            g = cls._from_symmetric_memory(world, rank, arena_bytes, device)
+            if g is not None:
+                return g
         g = cls(world, rank, arena_bytes, device, "ipc" if world > 1 else "local")
         with torch.cuda.device(device):
             p = ctypes.c_void_p()
@@ -88,6 +100,39 @@ class SiteGroup:
                     g.base[r] = q.value
                     g._opened.append(q.value)
                 dist.barrier()
+        g._reserve_flags()
+        return g
+
+    @classmethod
+    def _from_symmetric_memory(cls, world, rank, arena_bytes, device):
+        """VMM-backed arena with peer mappings and (where the fabric has it) an NVLS multicast mapping.  Every rank
+        must take the same decision, so success is agreed on with one all-reduce; on any failure the caller falls
+        back to the CUDA-IPC arena."""
+        import torch.distributed as dist
+        ok, t, h = 1, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            nbytes = (int(arena_bytes) + (2 << 20) - 1) // (2 << 20) * (2 << 20)
+            with torch.cuda.device(device):
+                t = symm.empty(nbytes, dtype=torch.uint8, device=device)
+                t.zero_()
+                torch.cuda.synchronize(device)
+                h = symm.rendezvous(t, dist.group.WORLD.group_name)
+            if len(h.buffer_ptrs) != world:
+                ok = 0
+        except Exception as e:      # noqa: BLE001  (API is private and may be missing / refuse this box)
+            from ..utils import logger
+            logger.warn(f"symmetric-memory arena unavailable ({type(e).__name__}: {e}); using the CUDA-IPC arena", True)
+            ok = 0
+        flag = torch.tensor([ok], device=device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) != 1:
+            return None
+        g = cls(world, rank, t.numel(), device, "symm")
+        g.base = [int(p) for p in h.buffer_ptrs]
+        g.mc_base = int(getattr(h, "multicast_ptr", 0) or 0)
+        g._symm = (t, h)
+        dist.barrier()
         g._reserve_flags()
         return g
 
@@ -119,6 +164,10 @@ class SiteGroup:
         off = self._layout[name][0]
         return [b + off for b in self.base]
 
+    def mc_ptr(self, name):
+        """Multicast address of a carved buffer (0 when the arena has no NVLS mapping)."""
+        return self.mc_base + self._layout[name][0] if self.mc_base else 0
+
     def local_view(self, name, site=None):
         return self.views(name)[self.rank if site is None else site]
 
@@ -128,7 +177,7 @@ class SiteGroup:
 
     @property
     def use_flags(self):
-        return self.backend == "ipc"
+        return self.backend in ("ipc", "symm")
 
     def close(self, barrier=None):
         """Unmap the peers' arenas, then free our own.  In ipc mode pass ``barrier`` (e.g.
@@ -146,3 +195,7 @@ class SiteGroup:
         for p in self._owned:
             l.dnb_arena_free(ctypes.c_void_p(p))
         self._opened, self._owned = [], []
+        if self._symm is not None:
+            self._symm = None                  # the allocator unmaps and frees once the tensor and handle are gone
+            if barrier is not None:
+                barrier()

@@ -67,7 +67,14 @@ class FusedDSGD:
         # one-shot pull below ~1 MB of gradients (pure latency regime)
         if mode == "auto":
             mode = "one_shot" if self.n * 4 <= (1 << 20) else "two_shot"
-        self.mode = {"two_shot": 0, "one_shot": 1}[mode]
+            # NVLS: reduce inside the NVSwitch and publish with one multicast store — per GPU 1/N of the buffer crosses
+            # NVLink each way instead of (N-1)/N.  (DINUNET_NVLS=0 keeps the P2P kernel on a multicast-capable arena.)
+            if (mode == "two_shot" and group.mc_base and group.nsites > 1 and optimizer != "none"
+                    and os.environ.get("DINUNET_NVLS", "1") != "0"):
+                mode = "nvls"
+        if mode == "nvls" and not (group.mc_base and group.nsites > 1):
+            raise ValueError("mode='nvls' needs a multi-GPU group whose arena has a multicast mapping")
+        self.mode = {"two_shot": 0, "one_shot": 1, "nvls": 2}[mode]
         self.params = group.alloc(f"{name}.params", self.n, torch.float32)
         self.grads = group.alloc(f"{name}.grads", self.n, wire_dtype)
         self.shadow = group.alloc(f"{name}.shadow", self.n, torch.bfloat16) if shadow_bf16 else None
@@ -156,7 +163,7 @@ class FusedDSGD:
         clears the staging buffer for the next step (no cast launch, no zero-fill launch).  Not for several
         simulated sites in one process: their kernels run one after the other, so every site's wire buffer has
         to be complete before the first kernel starts."""
-        return bool(self._grad_staging) and (self.group.backend == "ipc" or self.group.nsites == 1)
+        return bool(self._grad_staging) and (self.group.backend in ("ipc", "symm") or self.group.nsites == 1)
 
     def pack_grads(self, site=None):
         """16-bit wire only: cast the fp32 staging gradients into the peer-visible wire buffer."""
@@ -183,6 +190,9 @@ class FusedDSGD:
         d.out = self.out.data_ptr() if self.out is not None else None
         d.n, d.nranks, d.rank = self.n, g.nsites, site
         d.wire, d.mode, d.opt = _WIRE[self.wire_dtype], self.mode, self.opt
+        if self.mode == 2:
+            d.grads_mc, d.params_mc = g.mc_ptr(self._names[1]), g.mc_ptr(self._names[0])
+            d.shadow_mc = g.mc_ptr(self._names[2]) if self._names[2] else None
         d.use_flags = int(g.use_flags)
         d.beta1, d.beta2, d.eps = self.betas[0], self.betas[1], self.eps
         d.weight_decay, d.momentum = self.weight_decay, self.momentum

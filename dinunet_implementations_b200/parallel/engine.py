@@ -377,7 +377,7 @@ class DeviceEngine:
         import torch.distributed as dist
         self._graph = self._static_in = self._static_out = None
         torch.cuda.synchronize(self.device)
-        multi = self.group.backend == "ipc" and dist.is_available() and dist.is_initialized()
+        multi = self.group.backend in ("ipc", "symm") and dist.is_available() and dist.is_initialized()
         self.group.close(barrier=dist.barrier if multi else None)
         for o in getattr(self.fused, "opt", []) or []:
             if hasattr(o, "group"):

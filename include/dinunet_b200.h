@@ -74,7 +74,7 @@ typedef struct DnbDsgdDesc {
     long long n;                        /* flat length, multiple of 8 */
     int nranks, rank;
     int wire;                           /* 0 fp32, 1 bf16, 2 fp16 */
-    int mode;                           /* 0 two-shot (shard + push params), 1 one-shot (pull all) */
+    int mode;                           /* 0 two-shot (shard + push params), 1 one-shot (pull all), 2 two-shot over NVLS multicast */
     int opt;                            /* 0 Adam, 1 SGD(+momentum), 2 none (reduce only) */
     int use_flags;                      /* 0: no cross-GPU barrier (single-GPU emulation of S sites) */
     int step;                           /* optimiser step count t >= 1 (Adam bias correction) */
@@ -89,6 +89,13 @@ typedef struct DnbDsgdDesc {
                                            into grads[rank] itself before the barrier (each block packs exactly the elements
                                            the same-index block of every peer will read) — no separate cast launch */
     int zero_stage;                     /* also clear `stage` while packing: the next step needs no zero-fill launch */
+    /* mode 2 (NVLS): multicast (NVSwitch) addresses of the SAME symmetric gradient / parameter / shadow buffers.
+     * Rank r reduces its shard with multimem.ld_reduce (the switch adds the sites' values; 16-bit wires accumulate in
+     * fp32 and round once), applies the optimiser and publishes the updated values with multimem.st (one store
+     * reaches every site).  Per GPU 1/N of the buffer crosses NVLink each way instead of (N-1)/N. */
+    const void* grads_mc;
+    float* params_mc;
+    void* shadow_mc;
 } DnbDsgdDesc;
 int dnb_dsgd_fused_step(const DnbDsgdDesc* desc, void* stream);
 

@@ -29,7 +29,13 @@ def main():
     rank, world, local_rank = init_distributed_from_env()
     dev = torch.device(f"cuda:{local_rank}")
     n = 300007
-    for mode in ("two_shot", "one_shot"):
+    probe = SiteGroup.from_torch_distributed(1 << 20, dev)
+    has_mc = bool(probe.mc_base)
+    dist.barrier()
+    probe.close(barrier=dist.barrier)
+    if rank == 0:
+        print(f"arena backend: {probe.backend}, NVLS multicast mapping: {has_mc}", flush=True)
+    for mode in ("two_shot", "one_shot") + (("nvls",) if has_mc else ()):
         for wire in (torch.float32, torch.bfloat16):
             g = SiteGroup.from_torch_distributed(16 << 20, dev)
             f = FusedDSGD(g, n, wire_dtype=wire, lr=1e-2, mode=mode, shadow_bf16=True)
@@ -49,12 +55,14 @@ def main():
                 ref.grad = torch.stack([x.float() for x in gather(gr)]).mean(0)
                 opt.step()
             mine = f.params[rank][:n].clone()
-            assert torch.allclose(mine, ref.detach(), atol=2e-5, rtol=1e-5), (mode, wire, (mine - ref).abs().max())
+            # the switch rounds a 16-bit reduction once more (fp32 accumulate, 16-bit result): looser bound there
+            atol = 2e-3 if (mode == "nvls" and wire != torch.float32) else 2e-5
+            assert torch.allclose(mine, ref.detach(), atol=atol, rtol=1e-5), (mode, wire, (mine - ref).abs().max())
             for other in gather(mine):
                 assert torch.equal(other, mine), (mode, wire, "ranks diverged")
             assert torch.equal(f.shadow[rank][:n], mine.to(torch.bfloat16))
             dist.barrier()
-            g.close()
+            g.close(barrier=dist.barrier)
     if rank == 0:
         print("raw fused dSGD over IPC: OK", flush=True)
 
@@ -81,7 +89,7 @@ def main():
                           temporal_size=80, seed=4, precision_bits="16")
     tr.nn["net"].classifier[0].p = 0.0
     eng = DeviceEngine(tr, use_graph=True, graph_warmup=2)
-    assert eng.fused.mode == 0 and eng.fused.inkernel_pack, (eng.fused.mode, eng.fused.inkernel_pack)
+    assert eng.fused.mode in (0, 2) and eng.fused.inkernel_pack, (eng.fused.mode, eng.fused.inkernel_pack)
     gen = torch.Generator().manual_seed(3000 + rank)
     first = None
     for i in range(8):
