@@ -161,7 +161,7 @@ __device__ __forceinline__ void store8_f32(float* base, long long i, const float
 
 // NR = number of sites as a compile-time constant (1, 2, 4, 8: the peer loop unrolls exactly and the staging
 // registers are sized for it) or 0 = run-time count (any 1..8, guarded loop).
-template <int WIRE, int NR>
+template <int WIRE, int NR, bool NVLS>
 __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs a) {
     const int nranks = NR > 0 ? NR : a.nranks;
     // Step-dependent scalars come either from the launch arguments or — when the launch lives in a
@@ -211,11 +211,17 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
         hi = lo + per < a.n ? lo + per : a.n;
         if (lo > hi) lo = hi;
     }
-    for (long long i = lo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < hi; i += stride) {
+    // NVLS: the in-switch reduction of the NEXT element block is requested before this one is consumed (the round trip
+    // through the switch is longer than a peer load; with one block in flight per thread the links idle)
+    float gn[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const long long i_first = lo + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (NVLS && i_first < hi) mc_load_reduce8<WIRE>(a.grads_mc, i_first, gn);
+    for (long long i = i_first; i < hi; i += stride) {
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (a.mode == 2) {
-            // one instruction pair: the switch returns the sum over all sites
-            mc_load_reduce8<WIRE>(a.grads_mc, i, g);
+        if constexpr (NVLS) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = gn[k];
+            if (i + stride < hi) mc_load_reduce8<WIRE>(a.grads_mc, i + stride, gn);
         } else {
             // the loads of (up to) four peers are issued before the first add: 4 x 16-byte requests in flight per
             // thread, and the staging registers stay at 32 whatever the site count (the fixed summation order
@@ -278,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, 1) dsgd_fused_kernel(const DsgdArgs 
         sh.y = dnb::pack_bf16x2(p[2], p[3]);
         sh.z = dnb::pack_bf16x2(p[4], p[5]);
         sh.w = dnb::pack_bf16x2(p[6], p[7]);
-        if (a.mode == 2) {
+        if (NVLS) {
             // one multicast store reaches every site's copy (this one included)
             mc_store16(a.params_mc + i, __float_as_uint(p[0]), __float_as_uint(p[1]), __float_as_uint(p[2]), __float_as_uint(p[3]));
             mc_store16(a.params_mc + i + 4, __float_as_uint(p[4]), __float_as_uint(p[5]), __float_as_uint(p[6]), __float_as_uint(p[7]));
@@ -363,7 +369,11 @@ DNB_EXPORT int dnb_dsgd_fused_step(const DnbDsgdDesc* d, void* stream_) {
     if (blocks > kMaxBlocks) blocks = kMaxBlocks;
     if (blocks < 1) blocks = 1;
     const int nr = (d->nranks == 1 || d->nranks == 2 || d->nranks == 4 || d->nranks == 8) ? d->nranks : 0;
-#define DNB_DSGD_LAUNCH(W, N) DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<W, N>, dim3(blocks), dim3(kThreads), 0, stream, 0, a))
+#define DNB_DSGD_LAUNCH(W, N)                                                                                             \
+    do {                                                                                                              \
+        if (d->mode == 2) DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<W, N, true>, dim3(blocks), dim3(kThreads), 0, stream, 0, a));   \
+        else DNB_CUDA_CHECK(dnb_launch(dsgd_fused_kernel<W, N, false>, dim3(blocks), dim3(kThreads), 0, stream, 0, a));               \
+    } while (0)
 #define DNB_DSGD_WIRE(W)                                  \
     switch (nr) {                                         \
         case 1: DNB_DSGD_LAUNCH(W, 1); break;             \
