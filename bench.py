@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "recon-nccl", "recon-nccl-graph"])
     ap.add_argument("--no-compare", action="store_true", help="ours: skip the reconstructed-baseline arms after the timed loops")
     ap.add_argument("--compare-steps", type=int, default=15)
+    ap.add_argument("--compare-timeout", type=float, default=150.0, help="seconds after which the comparison arms are abandoned")
+    ap.add_argument("--main-timeout", type=float, default=900.0, help="seconds after which a stalled run exits with an error")
     ap.add_argument("--batch", type=int, default=16, help="per-site batch (reference local.py:33)")
     ap.add_argument("--precision-bits", default="16", choices=["16", "32"], help="gradient wire format")
     ap.add_argument("--hidden", type=int, default=384,
@@ -326,6 +328,12 @@ def main():
     from dinunet_implementations_b200.ops import native
     from dinunet_implementations_b200.parallel.engine import DeviceEngine, init_distributed_from_env, make_ica_trainer
 
+    def stalled():
+        sys.stderr.write(f"bench.py: no result after {args.main_timeout} s; giving up\n")
+        os._exit(3)
+    main_dog = threading.Timer(args.main_timeout, stalled)
+    main_dog.daemon = True
+    main_dog.start()
     rank, world, local_rank = init_distributed_from_env()
     if world != args.gpus:
         if rank == 0:
@@ -405,23 +413,63 @@ def main():
     if engine is not None:
         ranks_identical = params_identical(engine.params, world, device)
 
-    # ---- reconstructed baselines on the same box, same N, right after our timed loops (labelled as reconstructions) ----
+    clocks = sampler.stop(counted.get("mark0", 0), mark1) if sampler else None
+    value = world * args.batch * args.steps / (ms / 1e3)
+    out = {
+        "metric": "train samples/sec (ICA-LSTM dSGD, one site per GPU)", "value": value, "unit": "samples/s",
+        "impl": label, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "rounds_per_sec": args.steps / (ms / 1e3),
+        "higher_is_better": True, "scaling": "weak",
+        # BASELINE.md has no published samples/s (the reference cannot run here); the ratio is against the STRONGER
+        # reconstructed arm measured in this same run (its CUDA-graph replay), details under "baselines"
+        "vs_baseline": None,
+        "vs_baseline_def": "value / recon-nccl-graph value of this run (reconstructed baseline, not the reference itself)",
+        "baselines": None,
+        "dtype": "bf16" if not args.eager and args.impl == "ours" else "fp32",
+        "dtype_detail": ("bf16 tensor-core operands and gradient wire; fp32 accumulation (TMEM), fp32 master weights, "
+                         "optimizer state and saved cell states" if args.impl == "ours" and not args.eager else "fp32"),
+        "data": "synthetic", "gpu_launches": int(launches) if args.impl == "ours" else 0,
+        "gpu_launches_how": "host-side launch counter of the native library + counted graph replays x kernels recorded "
+                            "per captured graph, timed region only",
+        "ranks_identical": ranks_identical,
+        "clocks": clocks, "e2e": e2e,
+        "config": {"model": "ICALstm(input 256, hidden %d, comps 100, window 10, S 98, cls 2)" % args.hidden,
+                   "global_batch": world * args.batch, "seq_len": S, "parallelism": f"dp{world} (1 site per GPU)",
+                   "agg_engine": "dSGD", "precision_bits": args.precision_bits, "optimizer": "adam",
+                   "l2": "inputs rotate through a pool of %d MB > 126 MB L2" % (len(dev_pool) * bytes_in >> 20)},
+    }
+
+    # ---- reconstructed baselines on the same box, same N, right after our timed loops (labelled as reconstructions).
+    # They are context, not the product: a watchdog prints the already-measured line and ends the run if they stall.
     baselines = {}
     if engine is not None and not args.no_compare:
-        value_ours = world * args.batch * args.steps / (ms / 1e3)
+        def bail():
+            if rank == 0:
+                o = dict(out)
+                o["baselines"] = dict(baselines, note=f"comparison arms did not finish within {args.compare_timeout} s; skipped")
+                print(json.dumps(o), flush=True)
+            os._exit(0)
+        dog = threading.Timer(args.compare_timeout, bail)
+        dog.daemon = True
+        dog.start()
         for name, build in (("recon-nccl", lambda: build_recon_nccl(args, world, device)),
                             ("recon-nccl-graph", lambda: build_recon_nccl_graph(args, world, device, host_pool[0]))):
             try:
                 bstep, why = build()
             except Exception as e:      # noqa: BLE001
                 bstep, why = None, f"{type(e).__name__}: {e}"
-            if bstep is None:
-                baselines[name] = {"unavailable": why}
+            # every rank must take the same path from here on (the timed loops contain barriers)
+            okf = torch.tensor([0 if bstep is None else 1], device=device)
+            if world > 1:
+                import torch.distributed as dist
+                dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+            if int(okf.item()) == 0:
+                baselines[name] = {"unavailable": why or "unavailable on another rank"}
                 continue
             n = max(3, min(args.compare_steps, args.steps))
             bms, _ = timed_loop(bstep, dev_pool, n, 3, world, device)
             bval = world * args.batch * n / (bms / 1e3)
-            ent = {"value": bval, "unit": "samples/s", "ms_per_step": bms / n, "steps": n, "ratio": value_ours / bval,
+            ent = {"value": bval, "unit": "samples/s", "ms_per_step": bms / n, "steps": n, "ratio": value / bval,
                    "what": "reconstructed: the reference's own comps/icalstm/models.py + NCCL all_reduce + torch.optim.Adam"
                            + (", whole step replayed from one CUDA graph" if name.endswith("graph") else ", eager")}
             if e2e is not None:
@@ -434,35 +482,14 @@ def main():
             baselines[name] = ent
             del bstep
             torch.cuda.empty_cache()
+        dog.cancel()
 
-    clocks = sampler.stop(counted.get("mark0", 0), mark1) if sampler else None
     if rank == 0:
-        value = world * args.batch * args.steps / (ms / 1e3)
         strong = baselines.get("recon-nccl-graph", {}).get("value") or baselines.get("recon-nccl", {}).get("value")
-        out = {
-            "metric": "train samples/sec (ICA-LSTM dSGD, one site per GPU)", "value": value, "unit": "samples/s",
-            "impl": label, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "rounds_per_sec": args.steps / (ms / 1e3),
-            "higher_is_better": True, "scaling": "weak",
-            # BASELINE.md has no published samples/s (the reference cannot run here); the ratio is against the STRONGER
-            # reconstructed arm measured in this same run (its CUDA-graph replay), details under "baselines"
-            "vs_baseline": (value / strong) if strong else None,
-            "vs_baseline_def": "value / recon-nccl-graph value of this run (reconstructed baseline, not the reference itself)",
-            "baselines": baselines or None,
-            "dtype": "bf16" if not args.eager and args.impl == "ours" else "fp32",
-            "dtype_detail": ("bf16 tensor-core operands and gradient wire; fp32 accumulation (TMEM), fp32 master weights, "
-                             "optimizer state and saved cell states" if args.impl == "ours" and not args.eager else "fp32"),
-            "data": "synthetic", "gpu_launches": int(launches) if args.impl == "ours" else 0,
-            "gpu_launches_how": "host-side launch counter of the native library + counted graph replays x kernels recorded "
-                                "per captured graph, timed region only",
-            "ranks_identical": ranks_identical,
-            "clocks": clocks, "e2e": e2e,
-            "config": {"model": "ICALstm(input 256, hidden %d, comps 100, window 10, S 98, cls 2)" % args.hidden,
-                       "global_batch": world * args.batch, "seq_len": S, "parallelism": f"dp{world} (1 site per GPU)",
-                       "agg_engine": "dSGD", "precision_bits": args.precision_bits, "optimizer": "adam",
-                       "l2": "inputs rotate through a pool of %d MB > 126 MB L2" % (len(dev_pool) * bytes_in >> 20)},
-        }
-        print(json.dumps(out))
+        out["vs_baseline"] = (value / strong) if strong else None
+        out["baselines"] = baselines or None
+        print(json.dumps(out), flush=True)
+    main_dog.cancel()
     if engine is not None:
         engine.group.close()
     if world > 1:

@@ -67,10 +67,12 @@ class FusedDSGD:
         # one-shot pull below ~1 MB of gradients (pure latency regime)
         if mode == "auto":
             mode = "one_shot" if self.n * 4 <= (1 << 20) else "two_shot"
-            # NVLS: reduce inside the NVSwitch and publish with one multicast store — per GPU 1/N of the buffer crosses
-            # NVLink each way instead of (N-1)/N.  (DINUNET_NVLS=0 keeps the P2P kernel on a multicast-capable arena.)
+            # NVLS (opt-in, DINUNET_NVLS=1): reduce inside the NVSwitch and publish with one multicast store.  Per GPU the
+            # reduction then receives 1/N of the buffer and sends all of it, the broadcast the other way round, so the busier
+            # direction carries about what the P2P two-shot carries ((N-1)/N): measured at 2 GPUs it is not faster than the
+            # P2P kernel (profiles/r2_agg_microbench_2gpu.jsonl), so it is not the default.
             if (mode == "two_shot" and group.mc_base and group.nsites > 1 and optimizer != "none"
-                    and os.environ.get("DINUNET_NVLS", "1") != "0"):
+                    and os.environ.get("DINUNET_NVLS", "0") == "1"):
                 mode = "nvls"
         if mode == "nvls" and not (group.mc_base and group.nsites > 1):
             raise ValueError("mode='nvls' needs a multi-GPU group whose arena has a multicast mapping")
