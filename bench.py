@@ -22,6 +22,7 @@ Between timed iterations the inputs rotate through a pool larger than the 126 MB
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -480,7 +481,12 @@ def main():
                 ent["e2e_value"] = world * args.batch * n / (bwall / 1e3)
                 ent["e2e_ratio"] = e2e["value"] / ent["e2e_value"]
             baselines[name] = ent
+            # a CUDA graph that captured NCCL kernels must be gone before the communicator is torn down
+            if e2e is not None:
+                del b_e2e
             del bstep
+            gc.collect()
+            torch.cuda.synchronize()
             torch.cuda.empty_cache()
         dog.cancel()
 
@@ -490,6 +496,11 @@ def main():
         out["baselines"] = baselines or None
         print(json.dumps(out), flush=True)
     main_dog.cancel()
+    sys.stdout.flush()
+    # the result is out; a teardown that stalls (communicator / symmetric-memory release) must not hold the launcher
+    bye = threading.Timer(30.0, lambda: os._exit(0))
+    bye.daemon = True
+    bye.start()
     if engine is not None:
         engine.group.close()
     if world > 1:
