@@ -542,6 +542,10 @@ int static_scratch_for_current_device(float** out) {
 //    launch reads (rows < B, columns < N1), so stale contents are never consumed.
 //  * Because the array is shared, two calls whose kernels can overlap on the same GPU (different
 //    streams, or different host threads) race on it.  Issue them on one stream, or serialise them.
+//  * The address is the one of the CURRENT device: make the device that owns `stream` current before the
+//    call (a stream of another device gets that other device's launch with this device's pointer).
+//  * The cached address does not survive cudaDeviceReset(): a process that resets a device must not call
+//    this entry point on it again.
 DNB_EXPORT int dnb_head_backward_noalloc(const DnbHeadBwdDesc* d, void* stream_) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
     DNB_REQUIRE(d != nullptr, "dnb_head_backward_noalloc: null descriptor");

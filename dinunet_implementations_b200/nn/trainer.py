@@ -99,14 +99,16 @@ class NNTrainer:
                 self.nn[name] = torch.nn.DataParallel(self.nn[name], device_ids=[int(g) for g in gpus])
 
     def _init_optimizer(self):
-        first = next(iter(self.nn.values()))
+        # one optimiser over the parameters of EVERY module in self.nn: the engines flatten, exchange and assign
+        # gradients for all of them (distrib.trainable_params), so all of them have to be stepped
+        params = [p for m in self.nn.values() for p in m.parameters()]
         lr = float(self.cache.get("learning_rate", cfg.DEFAULT_ARGS["learning_rate"]))
         kind = str(self.cache.get("optimizer", "adam")).lower()
         if kind == "sgd":
-            self.optimizer["sgd"] = torch.optim.SGD(first.parameters(), lr=lr,
+            self.optimizer["sgd"] = torch.optim.SGD(params, lr=lr,
                                                     momentum=float(self.cache.get("momentum", 0.0)))
         else:
-            self.optimizer["adam"] = torch.optim.Adam(first.parameters(), lr=lr)
+            self.optimizer["adam"] = torch.optim.Adam(params, lr=lr)
 
     # ------------------------------------------------------------------ hooks
     def iteration(self, batch) -> dict:

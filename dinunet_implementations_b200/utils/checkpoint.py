@@ -50,8 +50,18 @@ def save_checkpoint(path: str, nn: dict, optimizer: dict | None = None, **extra)
 
 
 def load_checkpoint(path: str, nn: dict, optimizer: dict | None = None, map_location="cpu",
-                    load_optimizer_state: bool = True, strict: bool = True):
-    chk = torch.load(path, map_location=map_location, weights_only=False)
+                    load_optimizer_state: bool = True, strict: bool = True, trusted: bool = False):
+    """Checkpoints cross the site trust boundary (``pretrained_<site>.pt`` is written by another site and relayed
+    by the aggregator; ``pretrained_path`` is user supplied), so they are read with the restricted unpickler
+    (tensors, containers, strings, numbers: everything ``save_checkpoint`` writes).  ``trusted=True`` falls back
+    to full unpickling for a file this process's owner wrote with extra Python objects in it."""
+    try:
+        chk = torch.load(path, map_location=map_location, weights_only=True)
+    except Exception as e:      # noqa: BLE001  (pickle.UnpicklingError and friends)
+        if not trusted:
+            raise RuntimeError(f"{path}: not a plain tensor checkpoint ({type(e).__name__}: {e}); refusing to unpickle "
+                               "arbitrary objects from a file that may come from another site") from e
+        chk = torch.load(path, map_location=map_location, weights_only=False)
     if isinstance(chk, dict) and chk.get("source") == SOURCE_TAG:
         for name, model in nn.items():
             if name in chk["models"]:

@@ -225,7 +225,8 @@ int dnb_head_backward(const DnbHeadBwdDesc* desc, void* stream);
  * desc->dz1 is ignored and the [B,N1] scratch is a 128 KiB __device__ array inside the library,
  * held by every GPU that loads it.  Limits: B <= 64, N1 <= 512; anything larger is refused.  No
  * cudaMalloc/cudaFree.  The first call on a device looks up the array's device address — make it
- * before any stream capture on that device.  Calls share the array: overlapping calls on one GPU race. */
+ * before any stream capture on that device.  Calls share the array: overlapping calls on one GPU race.
+ * The device owning `stream` must be the current device; the cached address does not survive cudaDeviceReset. */
 int dnb_head_backward_noalloc(const DnbHeadBwdDesc* desc, void* stream);
 
 /* ---- K4: FreeSurfer MLP hidden layer backward through ReLU + BatchNorm(batch statistics)

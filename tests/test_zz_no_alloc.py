@@ -56,9 +56,23 @@ def _run(entry, t, dims, dz1):
     return rc, out
 
 
+def _torch_reference(t, dims):
+    """The same backward in plain fp32 PyTorch (the weights are bf16 values, everything else fp32)."""
+    B = dims[0]
+    W1, W2, W3 = t["W1"].float(), t["W2"].float(), t["W3"].float()
+    dl = t["dlogits"]
+    dz2 = (dl @ W3) * (t["a2"] > 0)
+    dy = (dz2 @ W2) * (t["a1"] > 0)
+    dxh = dy * t["bn_w"]
+    dz1 = t["invstd"] / B * (B * dxh - dxh.sum(0) - t["xhat"] * (dxh * t["xhat"]).sum(0))
+    return dict(dW3=dl.t() @ t["a2"], db3=dl.sum(0), dW2=dz2.t() @ t["a1"], db2=dz2.sum(0),
+                dbn_w=(dy * t["xhat"]).sum(0), dbn_b=dy.sum(0), dW1=dz1.t() @ t["a0"], db1=dz1.sum(0), dx=dz1 @ W1)
+
+
 def test_noalloc_head_backward_matches_caller_scratch_entry_point():
     from dinunet_implementations_b200.ops import native
     lib = native.require_gpu()
+    lib.dnb_last_error.restype = ctypes.c_char_p
     assert hasattr(lib, "dnb_head_backward_noalloc")
     # two calls in a row; the second is smaller, so the shared array still holds rows/columns
     # written by the first one
@@ -67,10 +81,44 @@ def test_noalloc_head_backward_matches_caller_scratch_entry_point():
         dz1 = torch.empty(dims[0], dims[2], device="cuda")
         rc_ref, ref = _run(lib.dnb_head_backward, t, dims, dz1)
         rc_new, new = _run(lib.dnb_head_backward_noalloc, t, dims, None)
-        assert rc_ref == 0 and rc_new == 0, native.lib().dnb_last_error
+        assert rc_ref == 0 and rc_new == 0, lib.dnb_last_error()
+        ref32 = _torch_reference(t, dims)
+        for k, v in ref32.items():                       # both entry points against plain fp32 PyTorch
+            s = max(v.abs().max().item(), 1e-3)
+            assert torch.allclose(new[k], v, atol=5e-3 * s + 1e-5), (dims, k, (new[k] - v).abs().max().item(), s)
         for k in ref:
             s = max(ref[k].abs().max().item(), 1e-3)
             assert torch.allclose(new[k], ref[k], atol=2e-3 * s + 1e-5), (dims, k, (new[k] - ref[k]).abs().max().item())
+
+
+def test_noalloc_call_allocates_no_device_memory():
+    """The point of the entry point: free device memory is the same before and after a call (the address lookup of
+    the first call has already happened above or happens in the warm-up call here)."""
+    from dinunet_implementations_b200.ops import native
+    lib = native.require_gpu()
+    dims = (16, 384, 256, 64, 2)
+    t = _inputs(*dims, 9)
+    outs = [_run(lib.dnb_head_backward_noalloc, t, dims, None)[1]]          # warm-up: resolves the symbol address
+    from dinunet_implementations_b200.ops.native import HeadBwdDesc
+    B, N0, N1, N2, N3 = dims
+    out = {k: torch.zeros_like(v) for k, v in outs[0].items()}
+    d = HeadBwdDesc()
+    for k in ("dlogits", "a0", "xhat", "invstd", "a1", "a2", "W1", "W2", "W3", "bn_w"):
+        setattr(d, k, t[k].data_ptr())
+    for k, v in out.items():
+        setattr(d, k, v.data_ptr())
+    d.training, d.accumulate = 1, 1
+    d.B, d.N0, d.N1, d.N2, d.N3 = dims
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(3):
+        assert lib.dnb_head_backward_noalloc(ctypes.byref(d), native.stream()) == 0
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, (free0, free1)
+    for k in out:
+        s = max(outs[0][k].abs().max().item(), 1e-3)
+        assert torch.allclose(out[k], 3 * outs[0][k], atol=6e-3 * s + 1e-5), k      # accumulate=1: three calls add up
 
 
 def test_noalloc_rejects_shapes_beyond_the_builtin_scratch():
