@@ -118,7 +118,8 @@ def test_noalloc_call_allocates_no_device_memory():
     assert free1 == free0, (free0, free1)
     for k in out:
         s = max(outs[0][k].abs().max().item(), 1e-3)
-        assert torch.allclose(out[k], 3 * outs[0][k], atol=6e-3 * s + 1e-5), k      # accumulate=1: three calls add up
+        mult = 1 if k == "dx" else 3          # accumulate=1: the parameter gradients of three calls add up, dx is overwritten
+        assert torch.allclose(out[k], mult * outs[0][k], atol=6e-3 * s + 1e-5), k
 
 
 def test_noalloc_rejects_shapes_beyond_the_builtin_scratch():
