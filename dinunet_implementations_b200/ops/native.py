@@ -291,3 +291,31 @@ class DadPackDesc(ctypes.Structure):
         ("N", ctypes.c_int * DAD_MAX_PACK), ("d", ctypes.c_int * DAD_MAX_PACK),
         ("count", ctypes.c_int),
     ]
+
+
+class PsgdDesc(ctypes.Structure):
+    _fields_ = [("grad", ctypes.c_void_p), ("E", ctypes.c_void_p), ("Q", ctypes.c_void_p), ("P", ctypes.c_void_p),
+                ("n", ctypes.c_int), ("m", ctypes.c_int), ("r", ctypes.c_int), ("pass_", ctypes.c_int)]
+
+
+def memset_async(t, value=0):
+    """``cudaMemsetAsync`` over a contiguous tensor on the current stream (no kernel launch)."""
+    l = require_gpu()
+    l.dnb_memset_async.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p]
+    assert t.is_contiguous()
+    check(l.dnb_memset_async(t.data_ptr(), int(value), t.numel() * t.element_size(), stream()), "dnb_memset_async")
+
+
+def seg_copy(pairs):
+    """``dst.copy_(src)`` for a list of ``(src, dst)`` contiguous fp32 tensor pairs in one launch (per 32 pairs)."""
+    if not pairs:
+        return
+    l = require_gpu()
+    k = len(pairs)
+    src = (ctypes.c_void_p * k)(*[s.data_ptr() for s, _ in pairs])
+    dst = (ctypes.c_void_p * k)(*[d.data_ptr() for _, d in pairs])
+    ln = (ctypes.c_int * k)(*[s.numel() for s, _ in pairs])
+    for s_, d_ in pairs:
+        assert s_.dtype == d_.dtype and s_.element_size() == 4 and s_.is_contiguous() and d_.is_contiguous() \
+            and s_.numel() == d_.numel()
+    check(l.dnb_seg_copy(src, dst, ln, ctypes.c_int(k), stream()), "dnb_seg_copy")

@@ -177,7 +177,7 @@ class FusedDSGD:
         if self.inkernel_pack and self._stage_clean:
             return                                  # the last aggregation left the staging gradients at zero
         for s in ([site] if site is not None else self.sites_here()):
-            (self._grad_staging[s] if self._grad_staging else self.grads[s]).zero_()
+            native.memset_async(self._grad_staging[s] if self._grad_staging else self.grads[s])
 
     # ------------------------------------------------------------------ the step
     def _desc(self, site, state_ix):

@@ -105,7 +105,14 @@ class _LocalOptim:
 
 
 class DevicePowerSGD:
-    """powerSGD across the sites of ``group``; ``site_params[s]`` = ordered parameter list of site s."""
+    """powerSGD across the sites of ``group``; ``site_params[s]`` = ordered parameter list of site s.
+
+    Per step and site, all on kernels of this library, all buffers allocated here once:
+    pass P per matrix (``E += grad``, ``P = M·Q`` in one sweep) + one segment-copy launch for the dense (1-D)
+    gradients → all-reduce(P) → batched orthogonalisation → memset + pass Q per matrix → all-reduce(Q) → finish per
+    matrix (``grad = P̂·Q̄ᵀ`` formed on the fly, ``E = M − M̂``) + one segment-copy launch → fused Adam/SGD.
+    ``csrc/psgd.cu`` explains why these are HBM-streaming kernels and not tensor-core GEMMs (rank <= 8: ~1 flop/byte).
+    """
 
     def __init__(self, group: SiteGroup, site_params, rank=4, lr=1e-3, optimizer="adam", momentum=0.0, seed=0):
         self.group, self.rank = group, int(rank)
@@ -118,6 +125,8 @@ class DevicePowerSGD:
         self.vec_ix = [i for i, p in enumerate(p0) if p.dim() < 2]
         self.shape2d = [(p0[i].shape[0], p0[i].numel() // p0[i].shape[0]) for i in self.mat_ix]
         self.r = [max(1, min(self.rank, n, m)) for n, m in self.shape2d]
+        if max(self.r) > 8:
+            raise ValueError("device powerSGD supports rank <= 8")
         # payload layouts (offsets aligned to 8 floats)
         self.p_off, cur = [], 0
         for (n, m), r in zip(self.shape2d, self.r):
@@ -133,60 +142,76 @@ class DevicePowerSGD:
             qcur += _r8(m * r)
         self.xp = _Exchange(group, cur, "psgd_p")
         self.xq = _Exchange(group, qcur, "psgd_q")
-        # per-site state: Q (fp32 [m,r]) identical on all sites, error feedback E (fp32 [n,m])
-        self.Q = [[lowrank.psgd_init_q(sh, r, seed + 17 * k, dev) for k, (sh, r) in enumerate(zip(self.shape2d, self.r))]
-                  for _ in self.sites]
+        # per-site state: Q (fp32, flat, same layout as the Q exchange) identical on all sites, error feedback E
+        self.Qflat = [torch.zeros(self.xq.red.n, device=dev) for _ in self.sites]
+        for qf in self.Qflat:
+            for k, (sh, r) in enumerate(zip(self.shape2d, self.r)):
+                qf[self.q_off[k]:self.q_off[k] + sh[1] * r].copy_(lowrank.psgd_init_q(sh, r, seed + 17 * k, dev).reshape(-1))
         self.E = [[torch.zeros(n, m, device=dev) for (n, m) in self.shape2d] for _ in self.sites]
+
+    @property
+    def Q(self):
+        """Per site, per matrix: the warm-start ``Q [m, r]`` (views into the flat state)."""
+        return [[qf[self.q_off[k]:self.q_off[k] + sh[1] * r].view(sh[1], r) for k, (sh, r) in enumerate(zip(self.shape2d, self.r))]
+                for qf in self.Qflat]
 
     def zero_grad(self, site=None):
         for li, s in enumerate(self.sites):
             if site is None or s == site:
-                self.opt[li].flat_grad.zero_()
+                native.memset_async(self.opt[li].flat_grad)
+
+    def _pass(self, which, li, k, grad, P, Q):
+        lib = native.require_gpu()
+        n, m = self.shape2d[k]
+        d = native.PsgdDesc()
+        d.grad, d.E, d.Q, d.P = grad.data_ptr(), self.E[li][k].data_ptr(), Q.data_ptr(), P.data_ptr()
+        d.n, d.m, d.r, d.pass_ = n, m, self.r[k], which
+        native.check(lib.dnb_psgd_pass(ctypes.byref(d), native.stream()), f"dnb_psgd_pass({which})")
+
+    def _grad2d(self, p):
+        g = p.grad
+        if not g.is_contiguous():
+            raise ValueError("powerSGD device kernels need contiguous gradients")
+        return g
 
     def step(self):
-        S = len(self.sites)
-        Mb, MbT = [[] for _ in range(S)], [[] for _ in range(S)]
-        # ---- phase P: M = grad + E ; P = M·Q ; dense 1-D grads ride along
+        # ---- pass P (+ dense gradients into the same exchange buffer)
         for li, s in enumerate(self.sites):
             ps = self.opt[li].params
             pay = self.xp.payload[s]
             for k, i in enumerate(self.mat_ix):
                 n, m = self.shape2d[k]
                 r = self.r[k]
-                E = self.E[li][k]
-                E.add_(ps[i].grad.view(n, m))                                  # E now holds M
-                mb = _bf16_pad_cols(E)
-                Mb[li].append(mb)
-                MbT[li].append(transpose_bf16(mb))                             # [m, n] for Q = Mᵀ·P̂
-                qt = _bf16_pad_cols(self.Q[li][k].t().contiguous())            # [r, m]
-                gemm_bf16(mb, qt, out=pay[self.p_off[k]:self.p_off[k] + n * r].view(n, r))
-            for j, i in enumerate(self.vec_ix):
-                pay[self.v_off[j]:self.v_off[j] + ps[i].numel()].copy_(ps[i].grad.reshape(-1))
+                self._pass(0, li, k, self._grad2d(ps[i]), pay[self.p_off[k]:self.p_off[k] + n * r],
+                           self.Qflat[li][self.q_off[k]:self.q_off[k] + m * r])
+            native.seg_copy([(ps[i].grad.reshape(-1), pay[self.v_off[j]:self.v_off[j] + ps[i].numel()])
+                             for j, i in enumerate(self.vec_ix)])
         Pm = self.xp.mean()
-        # ---- orthogonalise, Q = Mᵀ·P̂
+        # ---- orthogonalise, pass Q
         for li, s in enumerate(self.sites):
             mats = [Pm[li][self.p_off[k]:self.p_off[k] + n * r].view(n, r)
                     for k, ((n, m), r) in enumerate(zip(self.shape2d, self.r))]
             orthogonalize_batch(mats)
             pay = self.xq.payload[s]
+            native.memset_async(pay)
             for k, ((n, m), r) in enumerate(zip(self.shape2d, self.r)):
-                pt = _bf16_pad_cols(mats[k].t().contiguous())                  # [r, n]
-                gemm_bf16(MbT[li][k], pt, out=pay[self.q_off[k]:self.q_off[k] + m * r].view(m, r))
+                self._pass(1, li, k, pay, mats[k], pay[self.q_off[k]:self.q_off[k] + m * r])
         Qm = self.xq.mean()
-        # ---- finish: M̂ = P̂·Q̄ᵀ -> grad ; E = M − M̂ ; dense grads ; optimiser
+        # ---- finish: grad = P̂·Q̄ᵀ, E = M − M̂; dense gradients back; warm start; optimiser
+        lib = native.require_gpu()
+        lib.dnb_copy_async.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p]
         for li, s in enumerate(self.sites):
             ps = self.opt[li].params
             for k, i in enumerate(self.mat_ix):
                 n, m = self.shape2d[k]
                 r = self.r[k]
-                P_hat = Pm[li][self.p_off[k]:self.p_off[k] + n * r].view(n, r)
-                Qk = Qm[li][self.q_off[k]:self.q_off[k] + m * r].view(m, r)
-                g = ps[i].grad.view(n, m)
-                gemm_bf16(_bf16_pad_cols(P_hat), _bf16_pad_cols(Qk), out=g)    # K = r (zero-filled to a k-tile)
-                self.E[li][k].sub_(g)
-                self.Q[li][k].copy_(Qk)          # in place: the warm start survives CUDA-graph replay
-            for j, i in enumerate(self.vec_ix):
-                ps[i].grad.copy_(Pm[li][self.v_off[j]:self.v_off[j] + ps[i].numel()].view_as(ps[i]))
+                self._pass(2, li, k, self._grad2d(ps[i]), Pm[li][self.p_off[k]:self.p_off[k] + n * r],
+                           Qm[li][self.q_off[k]:self.q_off[k] + m * r])
+            native.seg_copy([(Pm[li][self.v_off[j]:self.v_off[j] + ps[i].numel()], ps[i].grad.reshape(-1))
+                             for j, i in enumerate(self.vec_ix)])
+            # in place: the warm start survives CUDA-graph replay (plain device-to-device copy, no kernel)
+            native.check(lib.dnb_copy_async(self.Qflat[li].data_ptr(), Qm[li].data_ptr(), self.Qflat[li].numel() * 4, 3,
+                                            native.stream()), "copy Q")
             self.opt[li].step()
 
 
@@ -304,7 +329,7 @@ class DeviceRankDAD:
     def zero_grad(self, site=None):
         for li, s in enumerate(self.sites):
             if site is None or s == site:
-                self.opt[li].flat_grad.zero_()
+                native.memset_async(self.opt[li].flat_grad)
 
     # ------------------------------------------------------------------ operands
     def _operands(self, li, k, entries, packs):

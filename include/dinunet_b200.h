@@ -300,6 +300,27 @@ typedef struct DnbDadPackDesc {
 } DnbDadPackDesc;
 int dnb_dad_pack(const DnbDadPackDesc* desc, void* stream);
 
+/* ---- K3a / K3c: the three streaming passes of a device-mode powerSGD step (engine "powerSGD", reference
+ * comps/__init__.py:16; results nnlogs.ipynb:48-50) on one gradient matrix [n, m] (fp32, row-major, contiguous):
+ *   pass 0: E += grad (E then holds M = grad + error feedback); P[n,r] = M * Q[m,r]
+ *   pass 1: Q[m,r] += M^T * P[n,r]      (P orthonormalised; Q must be zero on entry: fp32 atomics over row blocks)
+ *   pass 2: grad = P * Q^T (the rank-r approximation, formed on the fly); E = M - grad
+ * r <= DNB_PSGD_MAX_RANK.  ~1 flop per byte: HBM-bound streaming kernels, exact fp32. */
+#define DNB_PSGD_MAX_RANK 8
+#define DNB_PSGD_MAX_SEGS 32
+typedef struct DnbPsgdDesc {
+    float* grad;          /* [n,m] in (pass 0) / out (pass 2) */
+    float* E;             /* [n,m] error feedback, updated in place */
+    float* Q;             /* [m,r] */
+    float* P;             /* [n,r] */
+    int n, m, r, pass;
+} DnbPsgdDesc;
+int dnb_psgd_pass(const DnbPsgdDesc* desc, void* stream);
+/* dst[i][0..len[i]) = src[i][0..len[i]) for `count` fp32 segments (host arrays of device pointers), one launch per 32 */
+int dnb_seg_copy(const float* const* src, float* const* dst, const int* len, int count, void* stream);
+/* cudaMemsetAsync on `stream` (a memset node inside a captured graph, no kernel launch) */
+int dnb_memset_async(void* p, int value, size_t bytes, void* stream);
+
 /* K9: device-side metric accumulators (reference hooks: new_metrics().add / new_averages().add,
  * comps/fs/__init__.py:58-61, comps/icalstm/__init__.py:64-68).  Appends column `col` of scores_in [B, ld]
  * and the labels to scores/labs (capacity cap), updates state = {cursor, tp, fp, tn, fn} (uint64) at
