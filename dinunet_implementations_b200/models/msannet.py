@@ -34,6 +34,11 @@ class MSANNet(nn.Module):
             d = h
         self.fc_out = nn.Linear(d, self.out_size)
 
+    def grad_overwrite_params(self):
+        """Parameters whose gradients the fused backward can STORE instead of accumulate (every one is written by
+        exactly one kernel per backward); ``fc_out`` goes through autograd and keeps accumulating."""
+        return [p for blk in self.layers for p in blk.parameters()]
+
     def forward_eager(self, x):
         for block in self.layers:
             x = block(x)
@@ -44,4 +49,10 @@ class MSANNet(nn.Module):
             from ..ops import mlp as _mlp
             if _mlp.supported(self, x):
                 return _mlp.msannet_forward(self, x)
+        if getattr(self, "_grad_overwrite", False) and self.training and torch.is_grad_enabled():
+            # the engine skips the zero-fill of these gradients because the fused backward overwrites them; the eager
+            # path (shape outside the fused envelope) accumulates, so clear them here
+            for p in self.grad_overwrite_params():
+                if p.grad is not None:
+                    p.grad.zero_()
         return self.forward_eager(x)

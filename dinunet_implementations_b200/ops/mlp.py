@@ -92,13 +92,17 @@ class _MSANHidden(torch.autograd.Function):
         daT = torch.zeros(d_out.shape[1], Bp, device=d_out.device, dtype=torch.float32)
         daT[:, :B].copy_(d_out.t())
         daT = daT[:, :B]
+        # engine-driven steps with one micro-batch per aggregation let the kernels STORE the parameter gradients
+        # (model._grad_overwrite): no zero-fill of the flat gradient buffer and no atomic read-modify-write of the
+        # [4096, 4096] weight gradients — with `accumulate` the weight-gradient GEMM was 108 us per wide layer
+        acc = not getattr(model, "_grad_overwrite", False)
         for li in range(len(model.layers) - 1, -1, -1):
             blk = model.layers[li]
             lin, bnm = blk[0], blk[1]
             aT_prev, xhatT, invstd, W = saved[li]
             dzT, dz = bn_relu_backward(daT, xhatT, bnm.weight.detach(), bnm.bias.detach(), invstd, B,
-                                       _grad_buf(bnm.weight), _grad_buf(bnm.bias), accumulate=True)
-            gemm_bf16(dzT, aT_prev, out=_grad_buf(lin.weight), accumulate=True, split_k=1)
+                                       _grad_buf(bnm.weight), _grad_buf(bnm.bias), accumulate=acc)
+            gemm_bf16(dzT, aT_prev, out=_grad_buf(lin.weight), accumulate=acc, split_k=1)
             if li > 0:
                 WT = transpose_bf16(W)                                                  # [K, N]
                 daT = torch.empty(W.shape[1], Bp, device=d_out.device, dtype=torch.float32)[:, :B]

@@ -136,6 +136,8 @@ class FusedDSGD:
             self._grad_staging = self._grad_staging or {}
             self._grad_staging[site] = staging
         shadow_map = {}
+        self._span = getattr(self, "_span", {})
+        self._span.update({id(p): (off, p.numel()) for p, off in zip(ps, offs)})
         with torch.no_grad():
             for p, off in zip(ps, offs):
                 n = p.numel()
@@ -173,11 +175,30 @@ class FusedDSGD:
             for s in ([site] if site is not None else self.sites_here()):
                 self.grads[s].copy_(self._grad_staging[s])
 
+    def set_overwritten(self, params):
+        """``params``: parameters whose gradients the model's kernels overwrite every step — ``zero_grad`` then clears
+        only the rest (merged into as few memsets as possible)."""
+        skip = sorted(self._span[id(p)] for p in params if id(p) in getattr(self, "_span", {}))
+        spans, cur = [], 0
+        for off, n in skip:
+            if off > cur:
+                spans.append((cur, off - cur))
+            cur = max(cur, off + (n + ALIGN - 1) // ALIGN * ALIGN)
+        if cur < self.n:
+            spans.append((cur, self.n - cur))
+        self._zero_spans = spans
+
     def zero_grad(self, site=None):
         if self.inkernel_pack and self._stage_clean:
             return                                  # the last aggregation left the staging gradients at zero
         for s in ([site] if site is not None else self.sites_here()):
-            native.memset_async(self._grad_staging[s] if self._grad_staging else self.grads[s])
+            buf = self._grad_staging[s] if self._grad_staging else self.grads[s]
+            spans = getattr(self, "_zero_spans", None)
+            if spans is None:
+                native.memset_async(buf)
+            else:
+                for off, n in spans:
+                    native.memset_async(buf[off:off + n])
 
     # ------------------------------------------------------------------ the step
     def _desc(self, site, state_ix):

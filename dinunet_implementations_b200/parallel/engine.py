@@ -114,6 +114,17 @@ class DeviceEngine:
                 for m in trainer.nn.values():
                     for sub in m.modules():
                         sub._bf16_shadow = shadow
+        # models whose fused backward can store (not accumulate) their parameter gradients: skip the zero-fill of those
+        # spans and the atomic read-modify-write in the kernels.  Only with one micro-batch per aggregation.
+        self._overwrite = []
+        if int(self.cache.get("local_iterations", 1) or 1) == 1 and self.agg_engine in ("dSGD", "powerSGD"):
+            for m in trainer.nn.values():
+                if getattr(m, "fused", False) and hasattr(m, "grad_overwrite_params"):
+                    m._grad_overwrite = True
+                    self._overwrite += list(m.grad_overwrite_params())
+            if self._overwrite:
+                for f in ([self.fused] if self.agg_engine == "dSGD" else [o.f for o in self.fused.opt]):
+                    f.set_overwritten(self._overwrite)
         self.steps = 0
         self._one = None
         self.timer = None
@@ -242,6 +253,12 @@ class DeviceEngine:
 
     def _accumulate_step(self, micro_batches):
         """``local_iterations`` > 1: accumulate the micro-batch gradients, then aggregate once."""
+        if self._overwrite:                      # accumulation needs accumulating kernels and a full zero-fill
+            for m in self.trainer.nn.values():
+                m._grad_overwrite = False
+            for f in ([self.fused] if self.agg_engine == "dSGD" else [o.f for o in self.fused.opt]):
+                f._zero_spans = None
+            self._overwrite = []
         self.trainer.train_mode()
         self.fused.zero_grad(site=self.site)
         its = []

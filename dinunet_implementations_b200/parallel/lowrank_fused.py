@@ -100,6 +100,9 @@ class _LocalOptim:
     def flat_grad(self):
         return self.f.grads[0]
 
+    def zero_grad(self):
+        self.f.zero_grad(site=0)
+
     def step(self):
         self.f.step()
 
@@ -158,7 +161,7 @@ class DevicePowerSGD:
     def zero_grad(self, site=None):
         for li, s in enumerate(self.sites):
             if site is None or s == site:
-                native.memset_async(self.opt[li].flat_grad)
+                self.opt[li].zero_grad()
 
     def _pass(self, which, li, k, grad, P, Q):
         lib = native.require_gpu()
@@ -329,7 +332,7 @@ class DeviceRankDAD:
     def zero_grad(self, site=None):
         for li, s in enumerate(self.sites):
             if site is None or s == site:
-                native.memset_async(self.opt[li].flat_grad)
+                self.opt[li].zero_grad()
 
     # ------------------------------------------------------------------ operands
     def _operands(self, li, k, entries, packs):
