@@ -131,6 +131,48 @@ __global__ void window_gather_kernel(const float* __restrict__ in, float* __rest
     }
 }
 
+// Device-resident batches: gather B rows of a feature table (and their labels) selected by a permutation that lives
+// on the device.  state = {cursor, blocks-done counter}: every launch reads rows perm[(cursor + b) % n_perm] and the
+// last block advances the cursor by B, so the identical launch can be replayed from a CUDA graph and still walks
+// through the epoch.  Replaces DataLoader + default_collate + a host-to-device copy per step
+// (reference comps/icalstm/__init__.py:36-38, comps/fs/__init__.py:33-39).
+__global__ void __launch_bounds__(256) batch_gather_kernel(const float* __restrict__ table, long long row_floats,
+                                                           const long long* __restrict__ labels,
+                                                           const long long* __restrict__ perm, long long n_perm,
+                                                           unsigned long long* state, int B, float* __restrict__ out,
+                                                           long long* __restrict__ labels_out,
+                                                           long long* __restrict__ index_out) {
+    dnb::pdl_wait();
+    const unsigned long long cursor = *reinterpret_cast<volatile unsigned long long*>(state);
+    const int b = blockIdx.y;
+    const long long row = perm[(cursor + (unsigned long long)b) % (unsigned long long)n_perm];
+    const float* src = table + row * row_floats;
+    float* dst = out + (long long)b * row_floats;
+    const long long i0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const long long stride = (long long)gridDim.x * blockDim.x * 4;
+    if ((row_floats & 3) == 0 && ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        for (long long i = i0; i < row_floats; i += stride)
+            *reinterpret_cast<float4*>(dst + i) = __ldcs(reinterpret_cast<const float4*>(src + i));
+    } else {
+        for (long long i = i0; i < row_floats; i += stride)
+            for (int k = 0; k < 4 && i + k < row_floats; ++k) dst[i + k] = src[i + k];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (labels_out && labels) labels_out[b] = labels[row];
+        if (index_out) index_out[b] = row;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned long long prev = atomicAdd(state + 1, 1ull);
+        if (prev == (unsigned long long)gridDim.x * gridDim.y - 1) {
+            state[1] = 0ull;
+            state[0] = cursor + (unsigned long long)B;
+            __threadfence();
+        }
+    }
+}
+
 // K6: softmax + cross-entropy (mean over the batch) forward, and its gradient, in one pass.
 // One warp per row; classes strided over lanes.  Small batches (the federated sites' 16-64 rows) run as ONE
 // CTA that loops over the rows and reduces the loss on-chip: no memset node, no atomics.  Larger batches
@@ -299,6 +341,22 @@ DNB_EXPORT int dnb_window_gather(const float* in, float* out, int N, int C, int 
     int blocks = dnb_ceil_div(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     window_gather_kernel<<<blocks, 256, 0, st>>>(in, out, N, C, T, S, W, stride);
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+DNB_EXPORT int dnb_batch_gather(const float* table, long long row_floats, const long long* labels, const long long* perm,
+                                long long n_perm, unsigned long long* state, int B, float* out, long long* labels_out,
+                                long long* index_out, void* stream_) {
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+    DNB_REQUIRE(table && perm && state && out && row_floats > 0 && n_perm > 0 && B > 0 && B <= 65535,
+                "dnb_batch_gather: bad arguments");
+    int bx = (int)((row_floats / 4 + 255) / 256);
+    if (bx < 1) bx = 1;
+    if (bx > 64) bx = 64;
+    DNB_CUDA_CHECK(dnb_launch(batch_gather_kernel, dim3(bx, B), dim3(256), 0, st, 0, table, row_floats, labels, perm, n_perm,
+                              state, B, out, labels_out, index_out));
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;

@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) psgd_p_smem_kernel(const float* __restric
         for (int k = 0; k < R; ++k) acc[k] = 0.f;
         const float* g = grad + (long long)i * m;
         float* e = E + (long long)i * m;
-#pragma unroll 2
+#pragma unroll 4
         for (int j = lane * 4; j < m; j += 128) {
             const float4 a = __ldcs(reinterpret_cast<const float4*>(g + j));
             const float4 b = *reinterpret_cast<const float4*>(e + j);
@@ -97,37 +97,53 @@ __global__ void __launch_bounds__(256) psgd_p_kernel(const float* __restrict__ g
 
 // ---- pass Q: a thread owns 4 consecutive columns (16-byte loads), a CTA a block of rows; fp32 atomics into the
 // (pre-zeroed) exchange buffer.  P̂ rows are warp-uniform loads.
-constexpr int kQRows = 64;
+constexpr int kQRows = 256;
 template <int R>
 __global__ void __launch_bounds__(256) psgd_q_vec_kernel(const float* __restrict__ E, const float* __restrict__ Phat,
                                                          float* __restrict__ Qout, int n, int m) {
+    // CTA = 64 column groups (4 columns each) x 4 row phases over a block of kQRows rows; the four phases are summed in
+    // shared memory, then one set of atomics per column group (the row blocks of different CTAs meet in Qout)
+    __shared__ float red[3][64][4 * R + 1];
     dnb::pdl_wait();
-    const int j = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int j = (blockIdx.x * 64 + tx) * 4;
     const int i0 = blockIdx.y * kQRows;
     const int i1 = min(n, i0 + kQRows);
-    if (j >= m) return;
     float acc[4][R];
 #pragma unroll
     for (int t = 0; t < 4; ++t)
 #pragma unroll
         for (int k = 0; k < R; ++k) acc[t][k] = 0.f;
+    if (j < m) {
 #pragma unroll 4
-    for (int i = i0; i < i1; ++i) {
-        const float4 mv = *reinterpret_cast<const float4*>(E + (long long)i * m + j);
-        const float* p = Phat + (long long)i * R;
+        for (int i = i0 + ty; i < i1; i += 4) {
+            const float4 mv = *reinterpret_cast<const float4*>(E + (long long)i * m + j);
+            const float* p = Phat + (long long)i * R;
 #pragma unroll
-        for (int k = 0; k < R; ++k) {
-            const float pk = __ldg(p + k);
-            acc[0][k] = fmaf(mv.x, pk, acc[0][k]);
-            acc[1][k] = fmaf(mv.y, pk, acc[1][k]);
-            acc[2][k] = fmaf(mv.z, pk, acc[2][k]);
-            acc[3][k] = fmaf(mv.w, pk, acc[3][k]);
+            for (int k = 0; k < R; ++k) {
+                const float pk = __ldg(p + k);
+                acc[0][k] = fmaf(mv.x, pk, acc[0][k]);
+                acc[1][k] = fmaf(mv.y, pk, acc[1][k]);
+                acc[2][k] = fmaf(mv.z, pk, acc[2][k]);
+                acc[3][k] = fmaf(mv.w, pk, acc[3][k]);
+            }
         }
     }
+    if (ty > 0) {
 #pragma unroll
-    for (int t = 0; t < 4; ++t)
+        for (int t = 0; t < 4; ++t)
 #pragma unroll
-        for (int k = 0; k < R; ++k) atomicAdd(Qout + (long long)(j + t) * R + k, acc[t][k]);
+            for (int k = 0; k < R; ++k) red[ty - 1][tx][t * R + k] = acc[t][k];
+    }
+    __syncthreads();
+    if (ty == 0 && j < m) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                atomicAdd(Qout + (long long)(j + t) * R + k,
+                          acc[t][k] + red[0][tx][t * R + k] + red[1][tx][t * R + k] + red[2][tx][t * R + k]);
+    }
 }
 
 __global__ void __launch_bounds__(256) psgd_q_kernel(const float* __restrict__ E, const float* __restrict__ Phat,
@@ -168,7 +184,7 @@ __global__ void __launch_bounds__(256) psgd_finish_smem_kernel(float* __restrict
         for (int k = 0; k < R; ++k) p[k] = __ldg(Phat + (long long)i * R + k);
         float* e = E + (long long)i * m;
         float* g = grad + (long long)i * m;
-#pragma unroll 2
+#pragma unroll 4
         for (int j = lane * 4; j < m; j += 128) {
             float4 mh = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -258,7 +274,7 @@ DNB_EXPORT int dnb_psgd_pass(const DnbPsgdDesc* d, void* stream_) {
         DNB_REQUIRE(d->grad && d->Q && d->P, "pass P needs grad, Q and P");
         if (fast) {
             int blocks = (d->n + 7) / 8;
-            if (blocks > sms * 2) blocks = sms * 2;      // persistent: every CTA stages Q once and walks many rows
+            if (blocks > sms * 3) blocks = sms * 3;      // persistent: every CTA stages Q once and walks many rows
             DNB_PSGD_R(psgd_p_smem_kernel, (const float*)d->grad, d->E, (const float*)d->Q, d->P, d->n, d->m, ldq);
         } else {
             int blocks = (d->n + 7) / 8;
@@ -269,7 +285,7 @@ DNB_EXPORT int dnb_psgd_pass(const DnbPsgdDesc* d, void* stream_) {
     } else if (d->pass == 1) {
         DNB_REQUIRE(d->P && d->Q, "pass Q needs P (orthonormalised) and the Q output");
         if (vec && (d->r == 1 || d->r == 2 || d->r == 4)) {
-            dim3 grid((d->m / 4 + 255) / 256, (d->n + kQRows - 1) / kQRows);
+            dim3 grid((d->m / 4 + 63) / 64, (d->n + kQRows - 1) / kQRows);
             switch (d->r) {
                 case 1: DNB_CUDA_CHECK(dnb_launch(psgd_q_vec_kernel<1>, grid, dim3(256), 0, st, 0, (const float*)d->E, (const float*)d->P, d->Q, d->n, d->m)); break;
                 case 2: DNB_CUDA_CHECK(dnb_launch(psgd_q_vec_kernel<2>, grid, dim3(256), 0, st, 0, (const float*)d->E, (const float*)d->P, d->Q, d->n, d->m)); break;
@@ -284,7 +300,7 @@ DNB_EXPORT int dnb_psgd_pass(const DnbPsgdDesc* d, void* stream_) {
         DNB_REQUIRE(d->grad && d->Q && d->P, "finish needs grad, P and Q");
         if (fast) {
             int blocks = (d->n + 7) / 8;
-            if (blocks > sms * 2) blocks = sms * 2;
+            if (blocks > sms * 3) blocks = sms * 3;
             DNB_PSGD_R(psgd_finish_smem_kernel, d->E, d->grad, (const float*)d->P, (const float*)d->Q, d->n, d->m, ldq);
         } else {
             long long work = (long long)d->n * d->m;

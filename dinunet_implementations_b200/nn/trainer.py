@@ -166,7 +166,15 @@ class NNTrainer:
             for ds in dataset_list or []:
                 if ds is None or len(ds) == 0:
                     continue
-                loader = self.data_handle.get_loader(handle_key=mode, dataset=ds, shuffle=False)
+                tbl = getattr(ds, "_device_table", None)
+                if tbl is not None:
+                    # device-resident split: consecutive slices of the table, same batching as the loader below
+                    bs, n = int(self.cache.get("batch_size", 16)), len(tbl)
+                    if n > 1 and n % bs == 1:
+                        bs += 1
+                    loader = (tbl.slice(lo, min(lo + bs, n)) for lo in range(0, n, bs))
+                else:
+                    loader = self.data_handle.get_loader(handle_key=mode, dataset=ds, shuffle=False)
                 its = []
                 for batch in loader:
                     it = self.iteration(batch)

@@ -149,6 +149,7 @@ class DeviceEngine:
         self._loss_ring = None
         self._fast = None
         self._pending = []
+        self._batcher = self._rgraph = self._rout = None
 
     # ------------------------------------------------------------------ training
     def to_device(self, batch):
@@ -250,6 +251,39 @@ class DeviceEngine:
             self.graph_replays += 1
             return self._static_out
         return self._step_body(dev_batch)
+
+    # ------------------------------------------------------------------ device-resident stepping
+    def attach_batcher(self, batcher):
+        """``batcher``: ``data.device.DeviceBatcher`` over this site's training split.  ``train_step_resident`` then
+        steps without touching the host's data path: the batch gather is one more kernel in front of the forward
+        pass (inside the captured graph), and no bytes cross PCIe per step."""
+        self._batcher = batcher
+        self._rgraph = self._rout = None
+
+    def train_step_resident(self):
+        b = self._batcher
+        b.tick()                                  # host bookkeeping only: reshuffles at pass boundaries
+        self.steps += 1
+        if self.use_graph and self._rgraph is None and self.steps > self.graph_warmup:
+            try:
+                from ..ops import native
+                g = torch.cuda.CUDAGraph()
+                n0 = native.launch_count()
+                with torch.cuda.graph(g):
+                    it = self._step_body(b.launch())
+                self.kernels_per_step = native.launch_count() - n0
+                self._rgraph, self._rout = g, it
+            except Exception as e:      # noqa: BLE001
+                from ..utils import logger
+                logger.warn(f"CUDA graph capture of the device-resident step failed ({type(e).__name__}: {e}); "
+                            "stepping kernel by kernel", True)
+                torch.cuda.synchronize()
+                self.use_graph = False
+        if self._rgraph is not None:
+            self._rgraph.replay()
+            self.graph_replays += 1
+            return self._rout
+        return self._step_body(b.launch())
 
     def _accumulate_step(self, micro_batches):
         """``local_iterations`` > 1: accumulate the micro-batch gradients, then aggregate once."""
@@ -393,6 +427,7 @@ class DeviceEngine:
         """Release the graph and the peer-mapped arenas (collective in multi-process runs)."""
         import torch.distributed as dist
         self._graph = self._static_in = self._static_out = None
+        self._rgraph = self._rout = None
         torch.cuda.synchronize(self.device)
         multi = self.group.backend in ("ipc", "symm") and dist.is_available() and dist.is_initialized()
         self.group.close(barrier=dist.barrier if multi else None)

@@ -206,16 +206,37 @@ class DeviceFederation:
                "best_val_epoch": 0, "time_spent_on_computation": [], "cumulative_total_duration": []}
         direction = cache.get("metric_direction", "maximize")
         best = None
+        # device-resident data path (default on a GPU): every split is uploaded once, batches are cut by a kernel inside
+        # the step's CUDA graph, evaluation walks slices of the table — no DataLoader, no per-step host-to-device copy
+        resident = torch.cuda.is_available() and bool(cache.get("device_resident", True))
+
+        def _table(ds):
+            if resident and ds is not None and len(ds) > 0:
+                from ..data.device import DeviceTable
+                ds._device_table = DeviceTable.from_dataset(ds, engine.device)
+            return ds
         if str(cache.get("mode", "train")).lower() == "train":
-            cycle = _Cycle(handle, handle.get_train_dataset(dataset_cls), cache)
-            val_ds = handle.get_validation_dataset(dataset_cls)
+            train_ds = handle.get_train_dataset(dataset_cls)
+            cycle = _Cycle(handle, train_ds, cache)
+            val_ds = _table(handle.get_validation_dataset(dataset_cls))
             steps, k = self._epoch_steps(cycle)
+            batcher = None
+            if resident and k == 1 and len(train_ds) > 0:
+                from ..data.device import DeviceBatcher, DeviceTable
+                batcher = DeviceBatcher(DeviceTable.from_dataset(train_ds, engine.device), int(cache.get("batch_size", 16)),
+                                        seed=int(cache.get("seed", 0)))
+                engine.attach_batcher(batcher)
+                steps = max(max(_gather(len(batcher))), 1)
+                out["data_path"] = {"mode": "device_resident", "h2d_bytes_once": batcher.table.h2d_bytes,
+                                    "h2d_bytes_per_step": 0, "h2d_bytes_per_pass": batcher.h2d_bytes_per_pass}
             vep = max(int(cache.get("validation_epochs", 1)), 1)
             for ep in range(1, int(cache["epochs"]) + 1):
                 t_ep = time.time()
                 cache["epoch"] = ep
                 for _ in range(steps):
-                    if k == 1:
+                    if batcher is not None:
+                        engine.train_step_resident()
+                    elif k == 1:
                         engine.train_step(cycle.next())
                     else:
                         engine.train_step(None, micro_batches=[cycle.next() for _ in range(k)])
@@ -237,7 +258,7 @@ class DeviceFederation:
             if out["best_val_epoch"] == 0:
                 trainer.save_checkpoint(name="best.pt")
             engine.load_checkpoint(name="best.pt")
-        test_ds = handle.get_test_dataset(dataset_cls)
+        test_ds = _table(handle.get_test_dataset(dataset_cls))
         lavg, lmet = trainer.evaluation("test", [test_ds], save_pred=True)       # this site alone
         gavg, gmet = self._merge(trainer, lavg, lmet)                            # all sites
         out[Key.TEST_METRICS] = [trainer.log_row(lavg, lmet)]

@@ -91,6 +91,15 @@ class FreeSurferDataset(COINNDataset):
         _, y = self.indices[ix]
         return {"inputs": torch.from_numpy(self._features[ix]), "labels": torch.tensor(y), "ix": torch.tensor(ix)}
 
+    def device_table(self, device):
+        """The split's 66-feature table on the GPU (one upload; reference ``comps/fs/__init__.py:33-39`` re-reads a
+        file per item)."""
+        import numpy as np
+        from ..data.device import DeviceTable
+        x = torch.from_numpy(np.stack(self._features).astype(np.float32)).to(device)
+        y = torch.as_tensor([int(y) for _, y in self.indices], dtype=torch.int64)
+        return DeviceTable(x.contiguous(), y.to(device))
+
 
 class FreeSurferTrainer(COINNTrainer):
     def _init_nn_model(self):

@@ -48,16 +48,39 @@ def load_timecourses(path):
 class ICADataset(COINNDataset):
     def __init__(self, **kw):
         super().__init__(**kw)
-        self.data = None
+        self._raw, self._data = None, None
         self.window_size = int(self.cache["window_size"])
         self.window_stride = int(self.cache["window_stride"])
         self.temporal_size = int(self.cache["temporal_size"])
         self.num_components = int(self.cache["num_components"])
 
     def _load_indices(self, files, **kw):
-        raw = load_timecourses(self.path(cache_key="data_file"))
-        self.data = window_view(raw, self.window_size, self.window_stride, self.temporal_size)
+        self._raw = load_timecourses(self.path(cache_key="data_file"))
+        self._data = None
         self.indices += [[int(ix), int(y)] for ix, y in files]
+
+    @property
+    def data(self):
+        """Host copy of the windows ``[N, S, C, W]`` — built on first use (the device path never needs it)."""
+        if self._data is None and getattr(self, "_raw", None) is not None:
+            self._data = window_view(self._raw, self.window_size, self.window_stride, self.temporal_size)
+        return self._data
+
+    @data.setter
+    def data(self, v):
+        self._data = v
+
+    def device_table(self, device):
+        """The split on the GPU: ONE upload of the subjects this split uses (raw ``[n, C, T]``), windows cut there by
+        the K10 gather kernel (``dnb_window_gather``) — the reference's Python double loop (``:29-32``) on the device."""
+        from ..data.device import DeviceTable
+        from ..ops.elementwise import window_gather
+        import numpy as _np
+        rows = _np.asarray([ix for ix, _ in self.indices], dtype=_np.int64)
+        raw = torch.from_numpy(_np.ascontiguousarray(self._raw[rows], dtype=_np.float32)).to(device)
+        x = window_gather(raw, self.window_size, self.window_stride, self.temporal_size)
+        y = torch.as_tensor([int(y) for _, y in self.indices], dtype=torch.int64)
+        return DeviceTable(x.contiguous(), y.to(device))
 
     def __getitem__(self, ix):
         data_index, y = self.indices[ix]

@@ -176,6 +176,13 @@ int dnb_transpose_bf16(const void* in, long long ldi, void* out, long long ldo, 
 int dnb_cast_f32_bf16(const float* in, void* out, long long n, void* stream);
 /* K10: [N,C,T] -> [N,S,C,W] windows (reference comps/icalstm/__init__.py:28-32) */
 int dnb_window_gather(const float* in, float* out, int N, int C, int T, int S, int W, int stride, void* stream);
+/* Device-resident batches (replaces DataLoader + collate + per-step H2D; reference comps/icalstm/__init__.py:36-38,
+ * comps/fs/__init__.py:33-39): out[b] = table[perm[(cursor + b) % n_perm]] for b < B, labels / row indices likewise;
+ * state = {cursor, block counter} (two uint64, zero-initialised) is advanced by B on the device, so one captured launch
+ * walks through the epoch when replayed.  labels, labels_out and index_out may be NULL. */
+int dnb_batch_gather(const float* table, long long row_floats, const long long* labels, const long long* perm,
+                     long long n_perm, unsigned long long* state, int B, float* out, long long* labels_out,
+                     long long* index_out, void* stream);
 /* K6: softmax + mean cross-entropy forward and gradient in one pass (reference
  * comps/icalstm/__init__.py:60-61, comps/fs/__init__.py:54-55).  prob / dlogits / loss may be NULL;
  * log_softmax_out != 0 writes log-probabilities into prob. */
