@@ -113,4 +113,10 @@ class ICALstm(nn.Module):
             from ..ops import icalstm_fused as _f
             if _f.supported(self, x):
                 return _f.icalstm_forward(self, x)
+            if not getattr(self, "_warned_eager", False):
+                self._warned_eager = True
+                from ..utils import logger
+                logger.warn(f"ICALstm: input {tuple(x.shape)} / hidden {self.lstm.hidden_size} per direction is outside the "
+                            "fused kernels' envelope (batch <= 64, hidden <= 256 per direction, input_size % 8 == 0); "
+                            "running the eager PyTorch time loop", True)
         return self.forward_eager(x)

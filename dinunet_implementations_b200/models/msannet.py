@@ -7,9 +7,10 @@ BatchNorm always normalises with *batch* statistics, also in eval (no running st
 ``state_dict`` keys are identical (``layers.<i>.0.weight``, ``layers.<i>.1.weight|bias``,
 ``fc_out.weight|bias``), so checkpoints interchange with the reference class.
 
-On a CUDA device with ``fused=True`` the whole network runs in the hand-written sm_100a
-kernels of ``ops.mlp`` (single-CTA whole-net kernel for small widths, tcgen05 GEMM + fused
-BN/ReLU for wide ones); the eager path below is the oracle.
+On a CUDA device with ``fused=True`` the network runs in hand-written sm_100a kernels: widths up to 256 at
+batch <= 64 (the reference's default 66-256-128-64-32-2) in ONE launch forward and ONE backward
+(``ops.mlp_small`` / ``csrc/mlp_small.cu``), wider nets per layer on the tcgen05 GEMM with a fused
+BatchNorm/ReLU epilogue (``ops.mlp``); other shapes fall back to the eager path below (logged once), which is also the oracle.
 """
 from __future__ import annotations
 
@@ -46,9 +47,16 @@ class MSANNet(nn.Module):
 
     def forward(self, x):
         if self.fused and x.is_cuda and not self.dropout_in:
-            from ..ops import mlp as _mlp
-            if _mlp.supported(self, x):
+            from ..ops import mlp as _mlp, mlp_small as _small
+            if _small.supported(self, x):        # default-size net: the whole network in one launch each way
+                return _small.msannet_small_forward(self, x)
+            if _mlp.supported(self, x):          # wide layers: tcgen05 GEMM with BatchNorm/ReLU epilogue per layer
                 return _mlp.msannet_forward(self, x)
+            if not getattr(self, "_warned_eager", False):
+                self._warned_eager = True
+                from ..utils import logger
+                logger.warn(f"MSANNet: shape {tuple(x.shape)} / widths {self.hidden_sizes} are outside the fused kernels' "
+                            "envelope (batch 2..256, widths multiple of 8); running the eager PyTorch path", True)
         if getattr(self, "_grad_overwrite", False) and self.training and torch.is_grad_enabled():
             # the engine skips the zero-fill of these gradients because the fused backward overwrites them; the eager
             # path (shape outside the fused envelope) accumulates, so clear them here

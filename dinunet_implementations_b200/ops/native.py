@@ -319,3 +319,22 @@ def seg_copy(pairs):
         assert s_.dtype == d_.dtype and s_.element_size() == 4 and s_.is_contiguous() and d_.is_contiguous() \
             and s_.numel() == d_.numel()
     check(l.dnb_seg_copy(src, dst, ln, ctypes.c_int(k), stream()), "dnb_seg_copy")
+
+
+MLP_SMALL_MAX_WIDTH, MLP_SMALL_MAX_BATCH, MLP_SMALL_MAX_LAYERS, MLP_SMALL_MAX_CLASSES = 256, 64, 8, 16
+
+
+class MlpSmallDesc(ctypes.Structure):
+    _L = MLP_SMALL_MAX_LAYERS
+    _fields_ = [
+        ("x", ctypes.c_void_p),
+        ("W", ctypes.c_void_p * _L), ("gamma", ctypes.c_void_p * _L), ("beta", ctypes.c_void_p * _L),
+        ("Wfc", ctypes.c_void_p), ("bfc", ctypes.c_void_p),
+        ("act", ctypes.c_void_p * _L), ("xhat", ctypes.c_void_p * _L), ("invstd", ctypes.c_void_p * _L),
+        ("logits", ctypes.c_void_p), ("dlogits", ctypes.c_void_p),
+        ("dW", ctypes.c_void_p * _L), ("dgamma", ctypes.c_void_p * _L), ("dbeta", ctypes.c_void_p * _L),
+        ("dWfc", ctypes.c_void_p), ("dbfc", ctypes.c_void_p), ("dx", ctypes.c_void_p),
+        ("width", ctypes.c_int * _L),
+        ("B", ctypes.c_int), ("in0", ctypes.c_int), ("L", ctypes.c_int), ("C", ctypes.c_int), ("accumulate", ctypes.c_int),
+        ("eps", ctypes.c_float),
+    ]

@@ -244,6 +244,40 @@ int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, lo
                          const float* beta, const float* invstd, int N, int B, void* dzT, long long ldzt, void* dz,
                          long long ldz, float* dgamma, float* dbeta, int accumulate, void* stream);
 
+/* ---- K4, default size: the whole FreeSurfer MLP (reference comps/fs/models.py:13-31; default 66-256-128-64-32-2,
+ * compspec.json:228-235) in one launch forward and one launch backward, one CTA, activations in shared memory.
+ * Hidden layer l: z = a W_l^T (W_l bf16 [width_l, width_{l-1}], no bias) -> BatchNorm with batch statistics (biased
+ * variance, also in eval) -> ReLU; then logits = a W_fc^T + b_fc.  The forward saves act / xhat / invstd per layer
+ * for the backward, which writes or adds to every parameter gradient (accumulate bit 0: hidden layers add, bit 1:
+ * fc_out adds) and optionally writes dx.
+ * Limits: 2 <= B <= 64, widths and input <= 256, <= 8 hidden layers, <= 16 classes. */
+#define DNB_MLP_SMALL_MAX_WIDTH 256
+#define DNB_MLP_SMALL_MAX_BATCH 64
+#define DNB_MLP_SMALL_MAX_LAYERS 8
+#define DNB_MLP_SMALL_MAX_CLASSES 16
+typedef struct DnbMlpSmallDesc {
+    const float* x;                                   /* [B, in0] fp32 */
+    const void* W[DNB_MLP_SMALL_MAX_LAYERS];          /* bf16 [width_l, width_{l-1}] */
+    const float* gamma[DNB_MLP_SMALL_MAX_LAYERS];
+    const float* beta[DNB_MLP_SMALL_MAX_LAYERS];
+    const void* Wfc; const float* bfc;                /* bf16 [C, width_last], fp32 [C] */
+    float* act[DNB_MLP_SMALL_MAX_LAYERS];             /* [B, width_l] post-ReLU (saved) */
+    float* xhat[DNB_MLP_SMALL_MAX_LAYERS];            /* [B, width_l] normalised pre-activations (saved) */
+    float* invstd[DNB_MLP_SMALL_MAX_LAYERS];          /* [width_l] */
+    float* logits;                                    /* [B, C] forward output */
+    const float* dlogits;                             /* [B, C] backward input */
+    float* dW[DNB_MLP_SMALL_MAX_LAYERS];
+    float* dgamma[DNB_MLP_SMALL_MAX_LAYERS];
+    float* dbeta[DNB_MLP_SMALL_MAX_LAYERS];
+    float* dWfc; float* dbfc;
+    float* dx;                                        /* optional [B, in0] */
+    int width[DNB_MLP_SMALL_MAX_LAYERS];
+    int B, in0, L, C, accumulate;
+    float eps;
+} DnbMlpSmallDesc;
+int dnb_mlp_small_forward(const DnbMlpSmallDesc* desc, void* stream);
+int dnb_mlp_small_backward(const DnbMlpSmallDesc* desc, void* stream);
+
 /* ---- K3b: in-place column orthonormalisation (modified Gram-Schmidt, fp32) of `count` tall-skinny
  * matrices P[i] of shape [n[i], r[i]] with leading dimension ld[i]; one CTA per matrix, one launch per
  * 32 matrices.  powerSGD's orthogonalise(P) and the rankDAD subspace iteration (engine names
