@@ -10,6 +10,11 @@ if ROOT not in sys.path:
 os.environ.setdefault("DINUNET_QUIET", "1")
 
 REFERENCE = os.environ.get("DINUNET_REFERENCE", "/root/reference")
+if not os.path.isdir(REFERENCE):
+    # the GPU boxes have no /root/reference: __graft_entry__.build() stages a verbatim copy (git-ignored) for them
+    _staged = os.path.join(ROOT, "baseline", "_ref", "reference_src")
+    if os.path.isdir(_staged):
+        REFERENCE = _staged
 
 
 def pytest_configure(config):

@@ -90,3 +90,43 @@ def test_fused_softmax_ce_and_helpers():
     rows, colsT = cast_time_major(x)
     r = x.reshape(4, 6, 15).permute(1, 0, 2).reshape(24, 15).to(torch.bfloat16)
     assert torch.equal(rows, r) and torch.equal(colsT, r.t())
+
+
+@pytest.mark.parametrize("B,S,hidden", [(16, 98, 384), (32, 98, 348)])
+def test_fused_icalstm_matches_the_reference_model_file(B, S, hidden, ref_ica_models):
+    """The fused CUDA path against the REFERENCE's own comps/icalstm/models.py (loaded by path, moved to the GPU) on the
+    benchmark shape — same state_dict, same input: logits, final states and every parameter gradient."""
+    from dinunet_implementations_b200.models import ICALstm
+    from dinunet_implementations_b200.ops import icalstm_fused
+    torch.manual_seed(5)
+    kw = dict(input_size=256, hidden_size=hidden, num_comps=100, window_size=10, num_cls=2)
+    ref = ref_ica_models.ICALstm(**kw).cuda()
+    with torch.no_grad():
+        for p in ref.parameters():
+            if p.dim() >= 2:
+                p.copy_(p.to(torch.bfloat16).float())
+    ours = ICALstm(fused=True, **kw).cuda()
+    ours.load_state_dict(copy.deepcopy(ref.state_dict()))          # checkpoints interchange with the reference class
+    for m in (ref, ours):
+        m.train()
+        m.classifier[0].p = 0.0
+    x = torch.randn(B, S, 100, 10, device="cuda")
+    y = torch.randint(0, 2, (B,), device="cuda")
+    assert icalstm_fused.supported(ours, x)
+    lo_r, (h_r, c_r) = ref(x)
+    lo_o, (h_o, c_o) = ours(x)
+    assert torch.allclose(lo_o, lo_r, atol=3e-2, rtol=3e-2), (lo_o - lo_r).abs().max()
+    assert torch.allclose(h_o, h_r, atol=3e-2) and torch.allclose(c_o, c_r, atol=6e-2)
+    torch.nn.functional.cross_entropy(lo_r, y).backward()
+    torch.nn.functional.cross_entropy(lo_o, y).backward()
+    torch.cuda.synchronize()
+    top = max(p.grad.abs().max().item() for p in ref.parameters())
+    worst = 0.0
+    for (n, pr), (_, po) in zip(ref.named_parameters(), ours.named_parameters()):
+        if pr.grad.abs().max().item() < 1e-4 * top:
+            continue
+        cos = torch.nn.functional.cosine_similarity(po.grad.flatten(), pr.grad.flatten(), dim=0).item()
+        rel = ((po.grad - pr.grad).norm() / pr.grad.norm()).item()
+        worst = max(worst, rel)
+        assert cos > 0.995 and rel < 0.1, (n, cos, rel)
+    print(f"worst relative gradient error vs the reference model file: {worst:.4f}")
