@@ -82,6 +82,8 @@ def test_whole_network_kernels_match_the_reference_model_file(hidden, B, in_size
     x = torch.rand(B, in_size, device="cuda")
     y = torch.randint(0, classes, (B,), device="cuda")
     assert mlp_small.supported(ours, x)
+    # as under the engine: the kernels read a persistent bf16 copy of the weights (no per-call cast launches)
+    ours._bf16_shadow = {id(p): p.detach().to(torch.bfloat16) for p in ours.parameters() if p.dim() >= 2}
     n0 = native.launch_count()
     xr, xo = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
     for rep in range(2):                                  # two backward passes: gradients accumulate like autograd's
