@@ -8,6 +8,10 @@
 
     python -m dinunet_implementations_b200.tools.nnlogs RUN [RUN ...] [--json]
 
+``--boxplot PREFIX`` additionally writes ``PREFIX_<metric>.svg`` box plots over the folds of every run (one box per
+run: e.g. from-scratch vs pre-trained, ``NB.ipynb:96-110,156,189``) and prints the mean best-validation / early-stop
+epoch per run (``NB.ipynb:200``).
+
 ``RUN`` is any of: a results zip, a node output directory (``…/output/remote/simulatorRun``), a
 task directory holding ``fold_<k>/``, or a work directory (searched for the remote's output).
 One table row per (run, fold), then mean ± std over folds per run.
@@ -139,13 +143,47 @@ def render(all_rows):
     return "\n".join(lines)
 
 
+def boxplots(all_rows, prefix, labels=None, metrics=("accuracy", "f1", "test_score", "best_val_epoch")):
+    """One SVG per metric, one box per run over its folds.  Returns the written paths and the per-run mean
+    best-validation epoch (the scratch-vs-pretrain early-stop comparison of ``NB.ipynb:200``)."""
+    from ..utils.plotter import svg_boxplot
+    runs = []
+    for r in all_rows:
+        if r["run"] not in runs:
+            runs.append(r["run"])
+    names = {run: (labels[i] if labels and i < len(labels) else
+                   (os.path.basename(os.path.normpath(run)) or f"run{i}")) for i, run in enumerate(runs)}
+    written = []
+    os.makedirs(os.path.dirname(os.path.abspath(prefix)) or ".", exist_ok=True)
+    for m in metrics:
+        groups = {names[run]: [r[m] for r in all_rows if r["run"] == run and isinstance(r.get(m), (int, float))] for run in runs}
+        svg = svg_boxplot(groups, title=f"{m} over folds")
+        if svg:
+            p = f"{prefix}_{m}.svg"
+            with open(p, "w") as f:
+                f.write(svg)
+            written.append(p)
+    epochs = {}
+    for run in runs:
+        ev = [r["best_val_epoch"] for r in all_rows if r["run"] == run and isinstance(r.get("best_val_epoch"), (int, float))]
+        if ev:
+            epochs[names[run]] = statistics.mean(ev)
+    return written, epochs
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
     ap.add_argument("runs", nargs="+")
     ap.add_argument("--json", action="store_true")
+    ap.add_argument("--boxplot", metavar="PREFIX", help="write PREFIX_<metric>.svg box plots over the folds of every run")
+    ap.add_argument("--labels", default=None, help="comma-separated run labels for the plots (e.g. scratch,pretrained)")
     a = ap.parse_args(argv)
     rows = [r for p in a.runs for r in summarise(p)]
     print(json.dumps(rows) if a.json else render(rows))
+    if a.boxplot:
+        written, epochs = boxplots(rows, a.boxplot, a.labels.split(",") if a.labels else None)
+        print("box plots:", ", ".join(written))
+        print("mean best-validation epoch per run:", ", ".join(f"{k} {v:.1f}" for k, v in epochs.items()))
     return rows
 
 

@@ -255,3 +255,32 @@ def test_fused_capture_pairs_reproduce_the_weight_gradients():
         # noise, so the scale is the magnitude of the summed terms, not of the (vanishing) result
         sb = max(bref.abs().max().item(), 1e-3 * D.float().abs().sum(0).max().item(), 1e-6)
         assert torch.allclose(D.float().sum(0), bref, atol=0.05 * sb), (key, "bias")
+
+
+def test_file_mode_rankdad_learner_on_a_fused_model(tmp_path):
+    """File-mode rankDAD on a CUDA site whose model runs the fused kernels (its nn.Linear modules are never called, so
+    module hooks cannot fire): the learner must take the (delta, activation) pairs from the fused backward instead of
+    shipping zero factors.  rank >= rows of the head pairs, so those layers reconstruct exactly."""
+    from dinunet_implementations_b200.distrib import lowrank
+    from dinunet_implementations_b200.distrib.rankdad import make_taps, CapturedTap
+    from dinunet_implementations_b200.models import ICALstm
+    torch.manual_seed(0)
+    kw = dict(input_size=32, hidden_size=64, num_comps=8, window_size=5, num_cls=2)
+    net = ICALstm(fused=True, **kw).cuda()
+    net.train(); net.classifier[0].p = 0.0
+    taps, covered = make_taps([net])
+    assert all(isinstance(t, CapturedTap) for t in taps) and net.fused
+    x = torch.randn(6, 7, 8, 5, device="cuda")
+    y = torch.randint(0, 2, (6,), device="cuda")
+    torch.nn.functional.cross_entropy(net(x)[0], y).backward()
+    torch.cuda.synchronize()
+    for tap in taps:
+        D, A = tap.pop()                               # fp32, ones column appended for the bias
+        assert D is not None, "a fused model must hand its pairs over"
+        w = tap.module.weight
+        G = D.t() @ A
+        s = max(w.grad.abs().max().item(), 1e-6)
+        assert torch.allclose(G[:, :-1], w.grad, atol=0.05 * s), (tuple(w.shape), (G[:, :-1] - w.grad).abs().max().item(), s)
+        d, a, _ = lowrank.dad_compress(D, A, 10, 5, 1e-3, 0)
+        if D.shape[0] <= 10:
+            assert torch.allclose(lowrank.dad_reconstruct(d, a), G, atol=1e-4 * max(G.abs().max().item(), 1e-6) + 1e-7)

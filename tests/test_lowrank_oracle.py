@@ -70,3 +70,27 @@ def test_powersgd_residual_plus_approx_is_input_and_exact_for_low_rank():
     Ms = [U @ V.t() for _ in range(S)]
     M_hat, _, Q = lr.psgd_oracle_step(Ms, [Q0] * S, r)
     assert torch.allclose(M_hat, U @ V.t(), atol=1e-8)
+
+
+def test_linear_taps_pair_each_call_with_its_own_delta():
+    """Two micro-batches (local_iterations = 2) and a module called in a time loop: delta^T . activation over the
+    stacked blocks must equal autograd's accumulated weight gradient (the bias rides along as the ones column)."""
+    import torch
+    from dinunet_implementations_b200.distrib.rankdad import _LinearTap
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(5, 3)
+    cell = torch.nn.Linear(4, 4)
+    taps = [_LinearTap(lin), _LinearTap(cell)]
+    lin.train(); cell.train()
+    for mb in range(2):
+        x = torch.randn(6, 5)
+        h = torch.zeros(6, 4)
+        for t in range(3):                              # the same module three times per forward
+            h = torch.tanh(cell(h) + lin(x)[:, :1])
+        (h.sum() / 2).backward()
+    for tap, mod in zip(taps, (lin, cell)):
+        D, A = tap.pop()
+        G = D.t() @ A
+        assert torch.allclose(G[:, :-1], mod.weight.grad, atol=1e-5), (G[:, :-1] - mod.weight.grad).abs().max()
+        assert torch.allclose(G[:, -1], mod.bias.grad, atol=1e-5)
+        assert tap.pop() == (None, None)

@@ -65,3 +65,25 @@ def test_ica_two_sites_cpu(tmp_path):
     assert out["phase"] == "success"
     assert os.path.exists(os.path.join(str(tmp_path / "work"),
                                        "output/remote/simulatorRun/ICA-Classification/fold_0/logs.json"))
+
+
+def test_nnlogs_boxplots_compare_runs_over_folds(tmp_path):
+    """Counterpart of NB.ipynb's 10-fold accuracy / F1 box plots and the scratch-vs-pretrain early-stop comparison."""
+    from dinunet_implementations_b200.tools import nnlogs
+    runs = []
+    for name, pre in (("scratch", False), ("pretrained", True)):
+        root = str(tmp_path / f"fs_{name}")
+        synthetic.make_fs_dataset(root, site_sizes=(45, 45), seed=4, effect=0.6)
+        ov = {"epochs": 3, "num_reducers": 0, "num_folds": 3, "num_workers": 0, "patience": 50}
+        if pre:
+            ov.update({"pretrain": True, "pretrain_args": {"epochs": 2, "batch_size": 16, "patience": 5}})
+        sim = Simulator.from_data_path(COMP, root, str(tmp_path / f"work_{name}"), num_sites=2, overrides=ov)
+        assert sim.run(max_rounds=8000)["phase"] == "success"
+        runs.append(str(tmp_path / f"work_{name}"))
+    rows = [r for p in runs for r in nnlogs.summarise(p)]
+    assert len(rows) == 6
+    written, epochs = nnlogs.boxplots(rows, str(tmp_path / "plots" / "cmp"), labels=["scratch", "pretrained"])
+    assert any(w.endswith("_accuracy.svg") for w in written) and any(w.endswith("_f1.svg") for w in written)
+    svg = open([w for w in written if w.endswith("_accuracy.svg")][0]).read()
+    assert svg.startswith("<svg") and "scratch" in svg and "pretrained" in svg and svg.count("<rect") >= 3
+    assert set(epochs) == {"scratch", "pretrained"}
