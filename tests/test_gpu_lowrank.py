@@ -267,20 +267,26 @@ def test_file_mode_rankdad_learner_on_a_fused_model(tmp_path):
     torch.manual_seed(0)
     kw = dict(input_size=32, hidden_size=64, num_comps=8, window_size=5, num_cls=2)
     net = ICALstm(fused=True, **kw).cuda()
-    net.train(); net.classifier[0].p = 0.0
+    twin = ICALstm(fused=True, **kw).cuda()               # same weights, ordinary (non-capturing) fused backward
+    twin.load_state_dict(net.state_dict())
+    for m in (net, twin):
+        m.train(); m.classifier[0].p = 0.0
     taps, covered = make_taps([net])
     assert all(isinstance(t, CapturedTap) for t in taps) and net.fused
     x = torch.randn(6, 7, 8, 5, device="cuda")
     y = torch.randint(0, 2, (6,), device="cuda")
     torch.nn.functional.cross_entropy(net(x)[0], y).backward()
+    torch.nn.functional.cross_entropy(twin(x)[0], y).backward()
     torch.cuda.synchronize()
-    for tap in taps:
+    ref = dict(twin.named_modules())
+    names = [n for n, m in net.named_modules() if isinstance(m, torch.nn.Linear)]
+    for name, tap in zip(names, taps):
         D, A = tap.pop()                               # fp32, ones column appended for the bias
         assert D is not None, "a fused model must hand its pairs over"
-        w = tap.module.weight
+        wg = ref[name].weight.grad
         G = D.t() @ A
-        s = max(w.grad.abs().max().item(), 1e-6)
-        assert torch.allclose(G[:, :-1], w.grad, atol=0.05 * s), (tuple(w.shape), (G[:, :-1] - w.grad).abs().max().item(), s)
+        s = max(wg.abs().max().item(), 1e-6)
+        assert torch.allclose(G[:, :-1], wg, atol=0.05 * s), (name, (G[:, :-1] - wg).abs().max().item(), s)
         d, a, _ = lowrank.dad_compress(D, A, 10, 5, 1e-3, 0)
         if D.shape[0] <= 10:
             assert torch.allclose(lowrank.dad_reconstruct(d, a), G, atol=1e-4 * max(G.abs().max().item(), 1e-6) + 1e-7)
