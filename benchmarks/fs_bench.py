@@ -63,6 +63,17 @@ def main():
         print(json.dumps({"config": "FS-MLP 66-256-128-64-32-2 dSGD", "impl": "ours", "n_gpus": world, "batch_per_site": a.batch,
                           "ms_per_step": round(ms / a.steps, 4), "samples_per_sec": round(world * a.batch * a.steps / (ms / 1e3), 1),
                           "our_kernels_per_step": eng.kernels_per_step, "graph": eng._graph is not None}), flush=True)
+    # the product path of parallel/federation.py: the split lives on the device, the batch gather is part of the graph,
+    # the host only replays (no per-step copies, no per-step Python data handling)
+    from dinunet_implementations_b200.data.device import DeviceTable, DeviceBatcher
+    tbl = DeviceTable(torch.rand(4096, 66, generator=g).to(dev), torch.randint(0, 2, (4096,), generator=g).to(dev))
+    eng.attach_batcher(DeviceBatcher(tbl, a.batch, seed=rank))
+    ms = timed(lambda b: eng.train_step_resident(), batches, a.steps, a.warmup, world, dev)
+    if rank == 0:
+        print(json.dumps({"config": "FS-MLP 66-256-128-64-32-2 dSGD", "impl": "ours (device-resident batches)", "n_gpus": world,
+                          "batch_per_site": a.batch, "ms_per_step": round(ms / a.steps, 4),
+                          "samples_per_sec": round(world * a.batch * a.steps / (ms / 1e3), 1),
+                          "our_kernels_per_step": eng.kernels_per_step, "graph": eng._rgraph is not None}), flush=True)
     eng.close()
     mod = None
     for base in (os.path.join(ROOT, "baseline", "_ref", "reference_src"), "/root/reference"):
