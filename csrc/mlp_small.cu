@@ -20,8 +20,6 @@ constexpr int kMaxW = DNB_MLP_SMALL_MAX_WIDTH;     // 256
 constexpr int kMaxB = DNB_MLP_SMALL_MAX_BATCH;     // 64
 constexpr int kMaxL = DNB_MLP_SMALL_MAX_LAYERS;    // 8
 constexpr int kMaxC = DNB_MLP_SMALL_MAX_CLASSES;   // 16
-constexpr int kBufFloats = kMaxW * kMaxB;          // one [feature][batch] plane
-constexpr int kSmemBytes = 2 * kBufFloats * 4 + kMaxB * kMaxC * 4;
 
 struct Args {
     const float* x;
@@ -54,16 +52,39 @@ __device__ __forceinline__ void put(float* p, float v, int acc) {
     else *p = v;
 }
 
+// ---- asynchronous staging of global data into shared memory (cp.async, 16 bytes per request) -------------------------
+// The first version of these kernels read weights and saved activations straight from global memory inside the inner
+// loops: every loop iteration then waits for an L2 round trip (~0.3 us), and the step took 0.24 ms for ~3 MFLOP.
+// Everything an inner loop touches is therefore staged into shared memory first — the next layer's weights while the
+// current layer computes (two buffers, when they fit).
+__device__ __forceinline__ void stage_async(void* smem_dst, const void* gsrc, int bytes, bool commit = true) {
+    const bool ok = ((reinterpret_cast<uintptr_t>(gsrc) | reinterpret_cast<uintptr_t>(smem_dst)) & 15) == 0;
+    const int n16 = ok ? bytes >> 4 : 0;
+    const uint32_t d0 = dnb::smem_u32(smem_dst);
+    const char* g = reinterpret_cast<const char*>(gsrc);
+    for (int i = threadIdx.x; i < n16; i += kThreads)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + i * 16), "l"(g + (long long)i * 16) : "memory");
+    // tail (and the whole block when misaligned): plain 2-byte copies, visible after the next __syncthreads
+    const unsigned short* gs = reinterpret_cast<const unsigned short*>(gsrc);
+    unsigned short* ds = reinterpret_cast<unsigned short*>(smem_dst);
+    for (int i = n16 * 8 + threadIdx.x; i < bytes >> 1; i += kThreads) ds[i] = gs[i];
+    if (commit) asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void stage_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // Shared-memory planes are batch-major: plane[b * width + f].  A thread that owns feature f then walks the batch with
 // conflict-free accesses (consecutive threads = consecutive f), and a warp that owns one output feature reads the
 // activations of one batch row with its lanes along k (consecutive words).
 //
-// nxt[b][f] = sum_k cur[b][k] * W[f][k]: one warp per output feature, lanes along k (the bf16 weight row is read as
-// consecutive 2-byte loads = coalesced whatever `in` is, e.g. 66), 16 batch rows per pass, shuffle reduction.
+// nxt[b][f] = sum_k cur[b][k] * W[f][k]: one warp per output feature, lanes along k, 16 batch rows per pass, shuffle
+// reduction.  W is the staged shared-memory copy (bf16, [out][in]).
 __device__ __forceinline__ void dense_fwd(const float* cur, float* nxt, const __nv_bfloat16* W, int in, int out, int B) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int f = warp; f < out; f += kThreads / 32) {
-        const __nv_bfloat16* w = W + (long long)f * in;
+        const __nv_bfloat16* w = W + f * in;
         for (int b0 = 0; b0 < B; b0 += 16) {
             float acc[16];
 #pragma unroll
@@ -85,20 +106,32 @@ __device__ __forceinline__ void dense_fwd(const float* cur, float* nxt, const __
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a) {
+// smem: [plane cur][plane nxt][W buffer 0][W buffer 1 (if dbl)];  plane = B * kMaxW floats, W buffer = kMaxW*kMaxW bf16
+__global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a, int dbl) {
     extern __shared__ __align__(16) float sm[];
+    const int B = a.B, plane = B * kMaxW;
     float* cur = sm;
-    float* nxt = sm + kBufFloats;
+    float* nxt = sm + plane;
+    __nv_bfloat16* const w0 = reinterpret_cast<__nv_bfloat16*>(sm + 2 * plane);
+    __nv_bfloat16* const w1 = dbl ? w0 + kMaxW * kMaxW : w0;
     dnb::pdl_wait();
-    const int B = a.B;
+    stage_async(w0, a.W[0], a.width[0] * a.in0 * 2);
     for (int i = threadIdx.x; i < a.in0 * B; i += kThreads) cur[i] = a.x[i];
-    __syncthreads();
     int in = a.in0;
 #pragma unroll 1
     for (int l = 0; l < a.L; ++l) {
         const int out = a.width[l];
-        dense_fwd(cur, nxt, a.W[l], in, out, B);
+        const bool more = l + 1 < a.L;
+        if (dbl && more) {                       // prefetch the next layer's weights into the other buffer
+            stage_async(((l + 1) & 1) ? w1 : w0, a.W[l + 1], a.width[l + 1] * out * 2);
+            stage_wait<1>();
+        } else {
+            stage_wait<0>();
+        }
         __syncthreads();
+        dense_fwd(cur, nxt, (dbl && (l & 1)) ? w1 : w0, in, out, B);
+        __syncthreads();
+        if (!dbl && more) stage_async(w0, a.W[l + 1], a.width[l + 1] * out * 2);   // overlaps the BatchNorm phase
         // BatchNorm over the batch (biased variance) + ReLU, one thread per feature
         for (int f = threadIdx.x; f < out; f += kThreads) {
             float s = 0.f;
@@ -136,22 +169,35 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a) {
+// smem: [da][dz][dl 4 KB][W buffer 0][W 1 (if dbl)][a_prev 0 (if stage_ap)][a_prev 1 (if stage_ap && dbl)]
+__global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a, int dbl, int stage_ap) {
     extern __shared__ __align__(16) float sm[];
+    const int B = a.B, C = a.C, acc = a.accumulate & 1, acc_fc = a.accumulate & 2, plane = B * kMaxW;
     float* da = sm;                       // [batch][feature] gradient w.r.t. the current layer's output
-    float* dz = sm + kBufFloats;          // [batch][feature] gradient w.r.t. its pre-BatchNorm values
-    float* dl = sm + 2 * kBufFloats;      // [batch][class]
+    float* dz = sm + plane;               // [batch][feature] gradient w.r.t. its pre-BatchNorm values
+    float* dl = sm + 2 * plane;           // [batch][class]
+    __nv_bfloat16* const w0 = reinterpret_cast<__nv_bfloat16*>(dl + kMaxB * kMaxC);
+    __nv_bfloat16* const w1 = dbl ? w0 + kMaxW * kMaxW : w0;
+    float* const ap0 = reinterpret_cast<float*>(w0 + (dbl ? 2 : 1) * kMaxW * kMaxW);
+    float* const ap1 = dbl ? ap0 + plane : ap0;
     dnb::pdl_wait();
-    const int B = a.B, C = a.C, acc = a.accumulate & 1, acc_fc = a.accumulate & 2;
-    const int last = a.L > 0 ? a.width[a.L - 1] : a.in0;
+    const int last = a.width[a.L - 1];
+    auto stage_layer = [&](int l, int slot) {
+        const int in = l > 0 ? a.width[l - 1] : a.in0;
+        stage_async(slot ? w1 : w0, a.W[l], a.width[l] * in * 2, false);
+        if (stage_ap) stage_async(slot ? ap1 : ap0, l > 0 ? a.act[l - 1] : a.x, B * in * 4, false);
+        asm volatile("cp.async.commit_group;" ::: "memory");       // one group per layer
+    };
+    stage_layer(a.L - 1, dbl ? ((a.L - 1) & 1) : 0);
     for (int i = threadIdx.x; i < B * C; i += kThreads) dl[i] = a.dlogits[i];
     __syncthreads();
-    const float* aL = a.L > 0 ? a.act[a.L - 1] : a.x;
+    const float* aL = a.act[a.L - 1];
     // fc_out: weight / bias gradients, gradient w.r.t. the last hidden activations
     for (int item = threadIdx.x; item < C * last; item += kThreads) {
         const int k = item % last, c = item / last;
         float s = 0.f;
-        for (int b = 0; b < B; ++b) s = fmaf(dl[b * C + c], aL[(long long)b * last + k], s);
+#pragma unroll 8
+        for (int b = 0; b < B; ++b) s = fmaf(dl[b * C + c], __ldg(aL + (long long)b * last + k), s);
         put(a.dWfc + item, s, acc_fc);
     }
     for (int c = threadIdx.x; c < C; c += kThreads) {
@@ -169,14 +215,17 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a
 #pragma unroll 1
     for (int l = a.L - 1; l >= 0; --l) {
         const int out = a.width[l], in = l > 0 ? a.width[l - 1] : a.in0;
-        // ReLU + BatchNorm backward, one thread per feature
+        const int slot = dbl ? (l & 1) : 0;
+        if (dbl && l > 0) stage_layer(l - 1, (l - 1) & 1);       // prefetch the next (lower) layer's operands
+        // ReLU + BatchNorm backward, one thread per feature (its saved values are read with several loads in flight)
         for (int f = threadIdx.x; f < out; f += kThreads) {
             const float g = a.gamma[l][f], istd = a.invstd[l][f];
             float s1 = 0.f, s2 = 0.f;
+#pragma unroll 8
             for (int b = 0; b < B; ++b) {
-                const float y = a.act[l][(long long)b * out + f];
+                const float y = __ldg(a.act[l] + (long long)b * out + f);
+                const float xh = __ldg(a.xhat[l] + (long long)b * out + f);
                 const float dy = y > 0.f ? da[b * out + f] : 0.f;
-                const float xh = a.xhat[l][(long long)b * out + f];
                 s1 += dy;
                 s2 = fmaf(dy, xh, s2);
                 dz[b * out + f] = dy;
@@ -184,31 +233,35 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a
             put(a.dgamma[l] + f, s2, acc);
             put(a.dbeta[l] + f, s1, acc);
             const float k0 = g * istd / (float)B;
+#pragma unroll 8
             for (int b = 0; b < B; ++b) {
-                const float xh = a.xhat[l][(long long)b * out + f];
+                const float xh = __ldg(a.xhat[l] + (long long)b * out + f);
                 dz[b * out + f] = k0 * ((float)B * dz[b * out + f] - s1 - xh * s2);
             }
         }
+        if (dbl && l > 0) stage_wait<1>();
+        else stage_wait<0>();
         __syncthreads();
-        // weight gradient dW[f][k] = sum_b dz[b][f] * a_prev[b][k]   (thread = one (f, k); k fastest: coalesced)
-        const float* ap = l > 0 ? a.act[l - 1] : a.x;
+        // weight gradient dW[f][k] = sum_b dz[b][f] * a_prev[b][k]   (thread = one (f, k); k fastest: coalesced stores)
+        const float* ap = stage_ap ? (slot ? ap1 : ap0) : (l > 0 ? a.act[l - 1] : a.x);
         for (int item = threadIdx.x; item < out * in; item += kThreads) {
             const int k = item % in, f = item / in;
             float s = 0.f;
-#pragma unroll 4
-            for (int b = 0; b < B; ++b) s = fmaf(dz[b * out + f], ap[(long long)b * in + k], s);
+#pragma unroll 8
+            for (int b = 0; b < B; ++b) s = fmaf(dz[b * out + f], ap[b * in + k], s);
             put(a.dW[l] + item, s, acc);
         }
         // gradient w.r.t. the previous activations da_prev[b][k] = sum_f dz[b][f] * W[f][k]
-        // (thread = column k x 8 batch rows; the weight reads are coalesced over k, dz reads are broadcasts)
+        // (thread = column k x 8 batch rows; staged weights: consecutive threads read consecutive bf16, dz reads broadcast)
         if (l > 0 || a.dx != nullptr) {
             const int nbg = (B + 7) >> 3;
+            const __nv_bfloat16* Ws = slot ? w1 : w0;
             for (int item = threadIdx.x; item < in * nbg; item += kThreads) {
                 const int k = item % in, b0 = (item / in) * 8;
                 float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                const __nv_bfloat16* w = a.W[l] + k;
+#pragma unroll 4
                 for (int f = 0; f < out; ++f) {
-                    const float wk = bf(w + (long long)f * in);
+                    const float wk = bf(Ws + f * in + k);
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         if (b0 + j < B) s[j] = fmaf(wk, dz[(b0 + j) * out + f], s[j]);
@@ -219,6 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a
             }
         }
         __syncthreads();
+        if (!dbl && l > 0) stage_layer(l - 1, 0);
     }
     if (a.dx != nullptr)
         for (int i = threadIdx.x; i < B * a.in0; i += kThreads) a.dx[i] = da[i];
@@ -252,15 +306,37 @@ int fill(const DnbMlpSmallDesc* d, Args& a, bool backward) {
     return 0;
 }
 
-template <typename K>
-int launch(K kernel, const Args& a, cudaStream_t st) {
-    static bool configured[2] = {false, false};
-    const int which = (void*)kernel == (void*)mlp_small_fwd_kernel ? 0 : 1;
-    if (!configured[which]) {
-        DNB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        configured[which] = true;
+constexpr int kWBytes = kMaxW * kMaxW * 2;
+constexpr int kSmemLimit = 227 * 1024;
+
+int launch_fwd(const Args& a, cudaStream_t st) {
+    const int plane = a.B * kMaxW * 4;
+    int dbl = 1;
+    int need = 2 * plane + 2 * kWBytes;
+    if (need > kSmemLimit) { dbl = 0; need = 2 * plane + kWBytes; }
+    static int configured = 0;
+    if (configured < need) {
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(mlp_small_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+        configured = kSmemLimit;
     }
-    DNB_CUDA_CHECK(dnb_launch(kernel, dim3(1), dim3(kThreads), kSmemBytes, st, 0, a));
+    DNB_CUDA_CHECK(dnb_launch(mlp_small_fwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl));
+    DNB_LAUNCH_CHECK();
+    dnb_count_launch(1);
+    return 0;
+}
+
+int launch_bwd(const Args& a, cudaStream_t st) {
+    const int plane = a.B * kMaxW * 4, fixed = 2 * plane + kMaxB * kMaxC * 4;
+    int dbl = 1, stage_ap = 1;
+    int need = fixed + 2 * kWBytes + 2 * plane;
+    if (need > kSmemLimit) { dbl = 0; need = fixed + kWBytes + plane; }
+    if (need > kSmemLimit) { stage_ap = 0; need = fixed + kWBytes; }
+    static int configured = 0;
+    if (configured < need) {
+        DNB_CUDA_CHECK(cudaFuncSetAttribute(mlp_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+        configured = kSmemLimit;
+    }
+    DNB_CUDA_CHECK(dnb_launch(mlp_small_bwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl, stage_ap));
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;
@@ -271,11 +347,11 @@ int launch(K kernel, const Args& a, cudaStream_t st) {
 DNB_EXPORT int dnb_mlp_small_forward(const DnbMlpSmallDesc* d, void* stream_) {
     Args a;
     if (int rc = fill(d, a, false)) return rc;
-    return launch(mlp_small_fwd_kernel, a, reinterpret_cast<cudaStream_t>(stream_));
+    return launch_fwd(a, reinterpret_cast<cudaStream_t>(stream_));
 }
 
 DNB_EXPORT int dnb_mlp_small_backward(const DnbMlpSmallDesc* d, void* stream_) {
     Args a;
     if (int rc = fill(d, a, true)) return rc;
-    return launch(mlp_small_bwd_kernel, a, reinterpret_cast<cudaStream_t>(stream_));
+    return launch_bwd(a, reinterpret_cast<cudaStream_t>(stream_));
 }
