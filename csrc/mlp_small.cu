@@ -107,13 +107,13 @@ __device__ __forceinline__ void dense_fwd(const float* cur, float* nxt, const __
 }
 
 // smem: [plane cur][plane nxt][W buffer 0][W buffer 1 (if dbl)];  plane = B * kMaxW floats, W buffer = kMaxW*kMaxW bf16
-__global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a, int dbl) {
+__global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a, int dbl, int wcap) {
     extern __shared__ __align__(16) float sm[];
     const int B = a.B, plane = B * kMaxW;
     float* cur = sm;
     float* nxt = sm + plane;
     __nv_bfloat16* const w0 = reinterpret_cast<__nv_bfloat16*>(sm + 2 * plane);
-    __nv_bfloat16* const w1 = dbl ? w0 + kMaxW * kMaxW : w0;
+    __nv_bfloat16* const w1 = dbl ? w0 + wcap : w0;
     dnb::pdl_wait();
     stage_async(w0, a.W[0], a.width[0] * a.in0 * 2);
     for (int i = threadIdx.x; i < a.in0 * B; i += kThreads) cur[i] = a.x[i];
@@ -170,15 +170,15 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_small_fwd_kernel(const Args a
 }
 
 // smem: [da][dz][dl 4 KB][W buffer 0][W 1 (if dbl)][a_prev 0 (if stage_ap)][a_prev 1 (if stage_ap && dbl)]
-__global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a, int dbl, int stage_ap) {
+__global__ void __launch_bounds__(kThreads, 1) mlp_small_bwd_kernel(const Args a, int dbl, int stage_ap, int wcap) {
     extern __shared__ __align__(16) float sm[];
     const int B = a.B, C = a.C, acc = a.accumulate & 1, acc_fc = a.accumulate & 2, plane = B * kMaxW;
     float* da = sm;                       // [batch][feature] gradient w.r.t. the current layer's output
     float* dz = sm + plane;               // [batch][feature] gradient w.r.t. its pre-BatchNorm values
     float* dl = sm + 2 * plane;           // [batch][class]
     __nv_bfloat16* const w0 = reinterpret_cast<__nv_bfloat16*>(dl + kMaxB * kMaxC);
-    __nv_bfloat16* const w1 = dbl ? w0 + kMaxW * kMaxW : w0;
-    float* const ap0 = reinterpret_cast<float*>(w0 + (dbl ? 2 : 1) * kMaxW * kMaxW);
+    __nv_bfloat16* const w1 = dbl ? w0 + wcap : w0;
+    float* const ap0 = reinterpret_cast<float*>(w0 + (dbl ? 2 : 1) * wcap);
     float* const ap1 = dbl ? ap0 + plane : ap0;
     dnb::pdl_wait();
     const int last = a.width[a.L - 1];
@@ -306,37 +306,49 @@ int fill(const DnbMlpSmallDesc* d, Args& a, bool backward) {
     return 0;
 }
 
-constexpr int kWBytes = kMaxW * kMaxW * 2;
 constexpr int kSmemLimit = 227 * 1024;
 
+// bf16 elements one weight buffer must hold: the largest layer of THIS network (the default net: 256 x 128 = 64 KB)
+int weight_capacity(const Args& a) {
+    int cap = 0, in = a.in0;
+    for (int l = 0; l < a.L; ++l) {
+        const int n = a.width[l] * in;
+        if (n > cap) cap = n;
+        in = a.width[l];
+    }
+    return (cap + 7) & ~7;
+}
+
 int launch_fwd(const Args& a, cudaStream_t st) {
-    const int plane = a.B * kMaxW * 4;
+    const int plane = a.B * kMaxW * 4, wcap = weight_capacity(a), kWBytes = wcap * 2;
     int dbl = 1;
     int need = 2 * plane + 2 * kWBytes;
     if (need > kSmemLimit) { dbl = 0; need = 2 * plane + kWBytes; }
+    DNB_REQUIRE(need <= kSmemLimit, "mlp_small forward: batch %d with these widths needs %d bytes of shared memory", a.B, need);
     static int configured = 0;
     if (configured < need) {
         DNB_CUDA_CHECK(cudaFuncSetAttribute(mlp_small_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
         configured = kSmemLimit;
     }
-    DNB_CUDA_CHECK(dnb_launch(mlp_small_fwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl));
+    DNB_CUDA_CHECK(dnb_launch(mlp_small_fwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl, wcap));
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;
 }
 
 int launch_bwd(const Args& a, cudaStream_t st) {
-    const int plane = a.B * kMaxW * 4, fixed = 2 * plane + kMaxB * kMaxC * 4;
+    const int plane = a.B * kMaxW * 4, fixed = 2 * plane + kMaxB * kMaxC * 4, wcap = weight_capacity(a), kWBytes = wcap * 2;
     int dbl = 1, stage_ap = 1;
     int need = fixed + 2 * kWBytes + 2 * plane;
     if (need > kSmemLimit) { dbl = 0; need = fixed + kWBytes + plane; }
     if (need > kSmemLimit) { stage_ap = 0; need = fixed + kWBytes; }
+    DNB_REQUIRE(need <= kSmemLimit, "mlp_small backward: batch %d with these widths needs %d bytes of shared memory", a.B, need);
     static int configured = 0;
     if (configured < need) {
         DNB_CUDA_CHECK(cudaFuncSetAttribute(mlp_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
         configured = kSmemLimit;
     }
-    DNB_CUDA_CHECK(dnb_launch(mlp_small_bwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl, stage_ap));
+    DNB_CUDA_CHECK(dnb_launch(mlp_small_bwd_kernel, dim3(1), dim3(kThreads), (size_t)need, st, 0, a, dbl, stage_ap, wcap));
     DNB_LAUNCH_CHECK();
     dnb_count_launch(1);
     return 0;

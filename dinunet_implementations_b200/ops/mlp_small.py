@@ -17,6 +17,12 @@ def supported(model, x):
         return False
     B = x.shape[0]
     ws = list(model.hidden_sizes)
+    # shared-memory budget of the single-CTA kernels: two activation planes + (backward) the logits gradient + one
+    # weight buffer for the largest layer; staging of more than that is optional and decided by the launcher
+    dims = [model.in_size] + ws
+    wcap = max(a * b for a, b in zip(dims[:-1], dims[1:])) if ws else 0
+    if 2 * B * native.MLP_SMALL_MAX_WIDTH * 4 + 4096 + 2 * ((wcap + 7) // 8 * 8) > 227 * 1024:
+        return False
     return (2 <= B <= native.MLP_SMALL_MAX_BATCH and 1 <= len(ws) <= native.MLP_SMALL_MAX_LAYERS
             and max(ws + [model.in_size]) <= native.MLP_SMALL_MAX_WIDTH and model.out_size <= native.MLP_SMALL_MAX_CLASSES
             and not model.dropout_in
