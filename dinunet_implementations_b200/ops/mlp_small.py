@@ -17,11 +17,13 @@ def supported(model, x):
         return False
     B = x.shape[0]
     ws = list(model.hidden_sizes)
-    # shared-memory budget of the single-CTA kernels: two activation planes + (backward) the logits gradient + one
-    # weight buffer for the largest layer; staging of more than that is optional and decided by the launcher
+    # shared-memory budget of the single-CTA kernels (mirrors launch_bwd in csrc/mlp_small.cu): da, dz and one staged
+    # a_prev plane, the logits gradient and one padded weight buffer for the largest layer must fit 227 KB
+    r4 = lambda n: (n + 3) // 4 * 4
     dims = [model.in_size] + ws
-    wcap = max(a * b for a, b in zip(dims[:-1], dims[1:])) if ws else 0
-    if 2 * B * native.MLP_SMALL_MAX_WIDTH * 4 + 4096 + 2 * ((wcap + 7) // 8 * 8) > 227 * 1024:
+    plane = r4(B) * (r4(max(dims)) + 4) * 4
+    wbytes = (max(r4(o) * ((i + 1) // 2 * 2 + 2) for i, o in zip(dims[:-1], dims[1:])) + 7) // 8 * 8 * 2 if ws else 0
+    if 3 * plane + 4096 + wbytes > 227 * 1024:
         return False
     return (2 <= B <= native.MLP_SMALL_MAX_BATCH and 1 <= len(ws) <= native.MLP_SMALL_MAX_LAYERS
             and max(ws + [model.in_size]) <= native.MLP_SMALL_MAX_WIDTH and model.out_size <= native.MLP_SMALL_MAX_CLASSES

@@ -250,7 +250,8 @@ int dnb_bn_relu_backward(const float* daT, long long ldd, const float* xhatT, lo
  * variance, also in eval) -> ReLU; then logits = a W_fc^T + b_fc.  The forward saves act / xhat / invstd per layer
  * for the backward, which writes or adds to every parameter gradient (accumulate bit 0: hidden layers add, bit 1:
  * fc_out adds) and optionally writes dx.
- * Limits: 2 <= B <= 64, widths and input <= 256, <= 8 hidden layers, <= 16 classes. */
+ * Limits: 2 <= B <= 64, widths and input <= 256, <= 8 hidden layers, <= 16 classes, and the working set (three
+ * activation planes + the largest layer's weights) must fit 227 KB of shared memory: batch <= 48 for the default net. */
 #define DNB_MLP_SMALL_MAX_WIDTH 256
 #define DNB_MLP_SMALL_MAX_BATCH 64
 #define DNB_MLP_SMALL_MAX_LAYERS 8

@@ -59,8 +59,9 @@ def test_msannet_fused_matches_eager(hidden, B):
         assert cos > 0.98 and rel < 0.2, (n, cos, rel)
 
 
-@pytest.mark.parametrize("hidden,B,in_size,classes", [([256, 128, 64, 32], 16, 66, 2), ([256, 128, 64, 32], 64, 66, 2),
-                                                      ([40, 24], 2, 17, 5), ([256] * 8, 33, 256, 16)])
+@pytest.mark.parametrize("hidden,B,in_size,classes", [([256, 128, 64, 32], 16, 66, 2), ([256, 128, 64, 32], 48, 66, 2),
+                                                      ([256, 128, 64, 32], 32, 66, 2), ([40, 24], 2, 17, 5),
+                                                      ([37, 21, 9], 5, 13, 3), ([128] * 8, 33, 128, 16)])
 def test_whole_network_kernels_match_the_reference_model_file(hidden, B, in_size, classes, ref_fs_models):
     """csrc/mlp_small.cu (one launch forward, one backward) against the REFERENCE's own comps/fs/models.py on CUDA in
     fp32; the weights are bf16-representable so the only difference is the summation order: tight bounds, every
