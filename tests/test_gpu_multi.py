@@ -48,3 +48,29 @@ def test_lowrank_engines_across_gpus():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "DeviceEngine rankDAD multi-site: OK" in r.stdout and "DeviceEngine powerSGD multi-site: OK" in r.stdout
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_dataparallel_inside_a_site():
+    """E6: ``gpus: [0, 1]`` wraps the site's model in nn.DataParallel (reference GUI "GPU IDs to use Eg. [0], [0,1]");
+    the replicas run the eager path, gradients come back to device 0 and the optimiser steps."""
+    from dinunet_implementations_b200.tasks.fs import FreeSurferTrainer
+    cache = {"task_id": "FS-Classification", "input_size": 66, "hidden_sizes": [64, 32], "num_class": 2,
+             "monitor_metric": "auc", "batch_size": 16, "learning_rate": 1e-2, "gpus": [0, 1], "seed": 1, "agg_engine": "dSGD"}
+    tr = FreeSurferTrainer(cache=cache, input={}, state={})
+    tr.init_nn()
+    assert isinstance(tr.nn["fs_net"], torch.nn.DataParallel)
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(16, 66, generator=g)
+    y = (x[:, :4].sum(1) > 2).long()
+    losses = []
+    tr.train_mode()
+    for _ in range(30):
+        for o in tr.optimizer.values():
+            o.zero_grad()
+        it = tr.iteration({"inputs": x, "labels": y, "ix": torch.arange(16)})
+        it["loss"].backward()
+        for o in tr.optimizer.values():
+            o.step()
+        losses.append(float(it["loss"].detach()))
+    assert losses[-1] < losses[0], losses
