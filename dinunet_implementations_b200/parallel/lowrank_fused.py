@@ -3,13 +3,13 @@ every payload kept in device memory and exchanged through the symmetric arenas.
 
 Math = ``distrib/lowrank.py`` (the oracle).  What runs where:
 
-* big products (``P = M·Q``, ``Q = Mᵀ·P̂``, ``M̂ = P̂·Qᵀ``, rankDAD reconstruction ``ΔᵀA``) — the
-  tcgen05/TMA GEMM (``ops.gemm``), bf16 operands, fp32 accumulation in TMEM;
-* orthogonalisation — ``dnb_orthogonalize_batch`` (one CTA per factor, all layers in one launch);
-* cross-site exchange — the reduce-only mode of the fused dSGD kernel pulling every peer's payload
-  over NVLink (deterministic summation order ⇒ bit-identical factors on all sites).  rankDAD's
-  all-gather of factors is expressed as the same sum: each site fills only its own slot of an
-  ``[S, payload]`` buffer, so the sum *is* the concatenation;
+* rankDAD — ``csrc/dad.cu``: one launch compresses every tapped layer (per-layer cluster subspace iteration on
+  tcgen05 / TMA) and all-gathers the factors into every peer's slot from its tail; a second launch recompresses the
+  stacked factors and runs the reconstruction GEMM into the flat gradient buffer;
+* powerSGD — ``csrc/psgd.cu``: three fused streaming passes per gradient matrix (``E += grad`` with ``P = M·Q``;
+  ``Q = Mᵀ·P̂``; on-the-fly ``M̂ = P̂·Q̄ᵀ`` with ``E = M − M̂``), the two all-reduces through the reduce-only mode of the
+  fused dSGD kernel (peer loads over NVLink, deterministic order ⇒ bit-identical factors on all sites), batched
+  orthogonalisation ``dnb_orthogonalize_batch``;
 * optimiser — the fused Adam/SGD kernel on the site's flat parameter buffer.
 
 Every object here drives all sites that live in this process: one with ``torchrun`` (ipc), all
@@ -24,8 +24,6 @@ import torch
 
 from ..distrib import lowrank
 from ..ops import native
-from ..ops.elementwise import cast_bf16, transpose_bf16
-from ..ops.gemm import gemm_bf16
 from .comm import SiteGroup
 from .dsgd_fused import FusedDSGD, flat_layout
 
@@ -48,14 +46,6 @@ def orthogonalize_batch(mats, eps: float = 1e-8):
         assert m.dtype == torch.float32 and m.stride(1) == 1
     native.check(lib.dnb_orthogonalize_batch(P, n, r, ld, ctypes.c_int(k), ctypes.c_float(eps), native.stream()),
                  "dnb_orthogonalize_batch")
-
-
-def _bf16_pad_cols(x: torch.Tensor, cols: int | None = None):
-    """fp32 ``[a, b]`` → bf16 with the leading dimension padded to a multiple of 8 (TMA row pitch)."""
-    a, b = x.shape
-    out = torch.zeros(a, _r8(cols or b), device=x.device, dtype=torch.bfloat16)
-    out[:, :b].copy_(x)
-    return out[:, :b]
 
 
 class _Exchange:
