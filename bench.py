@@ -319,6 +319,8 @@ def params_identical(params, world, device):
 def main():
     args = parse()
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return 0                                   # one line per job, not one per rank
         print(json.dumps({"impl": "reference", "unavailable":
                           "reference is a COINSTAC app whose engine packages (coinstac, coinstac-dinunet) are not "
                           "installed/installable offline and it has no setup.py/pyproject (pip: 'not installable'); "
