@@ -83,6 +83,7 @@ DEFAULT_ARGS = {
     "optimizer": "adam",
     "cpu_threads": "auto",
     "profile_enabled": False,
+    "device_resident": True,       # device mode: keep every split on the GPU and cut batches there (data/device.py)
     "verbose": False,
     "persist_logs": True,
 }
