@@ -104,7 +104,13 @@ def make_taps(nn_modules):
     the pairs over itself (``dad_capture_keys()`` → ``CapturedTap``) or is switched to its eager path."""
     taps, covered = [], set()
     for m in nn_modules:
-        keys = set(m.dad_capture_keys()) if (getattr(m, "fused", False) and hasattr(m, "dad_capture_keys")) else set()
+        # the fused path only ever runs on a CUDA device with the native library loaded; on a CPU site the model takes
+        # its eager path whatever `fused` says, and only module hooks see the pairs
+        on_gpu = any(p.is_cuda for p in m.parameters())
+        if on_gpu:
+            from ..ops import native
+            on_gpu = native.available()
+        keys = set(m.dad_capture_keys()) if (on_gpu and getattr(m, "fused", False) and hasattr(m, "dad_capture_keys")) else set()
         if keys:
             m._dad_capture = True
         elif hasattr(m, "fused"):

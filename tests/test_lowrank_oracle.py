@@ -94,3 +94,22 @@ def test_linear_taps_pair_each_call_with_its_own_delta():
         assert torch.allclose(G[:, :-1], mod.weight.grad, atol=1e-5), (G[:, :-1] - mod.weight.grad).abs().max()
         assert torch.allclose(G[:, -1], mod.bias.grad, atol=1e-5)
         assert tap.pop() == (None, None)
+
+
+def test_make_taps_uses_hooks_on_a_cpu_site_even_for_fused_capable_models():
+    """ICALstm defaults to fused=True, but on a CPU site its forward is the eager one: rankDAD must tap the nn.Linear
+    modules there (the fused hand-over only exists on CUDA)."""
+    import torch
+    from dinunet_implementations_b200.distrib.rankdad import make_taps, _LinearTap
+    from dinunet_implementations_b200.models import ICALstm
+    torch.manual_seed(0)
+    net = ICALstm(input_size=8, hidden_size=8, num_comps=3, window_size=4, num_cls=2, fused=True)
+    taps, covered = make_taps([net])
+    assert taps and all(isinstance(t, _LinearTap) for t in taps)
+    net.train()
+    x = torch.randn(4, 5, 3, 4)
+    torch.nn.functional.cross_entropy(net(x)[0], torch.tensor([0, 1, 0, 1])).backward()
+    for t in taps:
+        D, A = t.pop()
+        G = D.t() @ A
+        assert torch.allclose(G[:, :-1], t.module.weight.grad, atol=1e-5)
